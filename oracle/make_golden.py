@@ -1,0 +1,106 @@
+#!/usr/bin/env python
+"""Generate tests/golden/golden.npz from the reference's OWN code (oracle/_ref, i.e.
+/root/reference/src/{convolve,correlate,memory}.c compiled against the FFT shim).
+
+TEST INFRASTRUCTURE.  Run in the build container (needs /root/reference to have built
+oracle/_ref/libSimd_ref.so):   python oracle/make_golden.py
+The fixtures are committed; the GPU box and the CPU test-suite only read them.
+
+Each case stores x, h, the op ("convolve" | "correlate"), the reference entry point that
+produced `y` ("simd0" scalar loop, "simd1" AVX loop, "fft", "overlap_save", "auto" = the
+convolve_initialize / cross_correlate_initialize selector path) and the handle facts the
+reference reported (algorithm, L or M).
+"""
+import os
+import sys
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(os.path.dirname(HERE), "tests"))
+from _oracle import Reference  # noqa: E402
+
+ref = Reference()
+cases = {}
+
+
+def add(name, x, h, op, path, guard=0):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    h = np.ascontiguousarray(h, dtype=np.float32)
+    corr = op == "correlate"
+    xin = x
+    if guard:  # reference over-reads x in the first overlap-save block
+        buf = np.zeros(x.size + guard, dtype=np.float32)
+        buf[:x.size] = x
+        xin = buf[:x.size]
+    info = {}
+    if path == "simd0":
+        y = ref.simd(xin, h, correlate=corr, simd=0)
+    elif path == "simd1":
+        y = ref.simd(xin, h, correlate=corr, simd=1)
+    else:
+        kind = {"fft": "_fft", "overlap_save": "_overlap_save", "auto": ""}[path]
+        y, info = ref.handle_call(kind, xin, h, correlate=corr, return_handle_info=True)
+    cases[name] = dict(x=x, h=h, y=y, op=op, path=path, info=info)
+
+
+# --- known-answer tests: tests/convolve.cc:53-71, tests/correlate.cc:53-71
+kx = np.arange(1, 9, dtype=np.float32)
+kh = np.array([10, 9, 8, 7], dtype=np.float32)
+add("kat_convolve", kx, kh, "convolve", "simd0")
+add("kat_correlate", kx, kh, "correlate", "simd0")
+assert cases["kat_convolve"]["y"].tolist() == [10, 29, 56, 90, 124, 158, 192, 226, 170, 113, 56]
+assert cases["kat_correlate"]["y"].tolist() == [7, 22, 46, 80, 114, 148, 182, 216, 187, 142, 80]
+
+# --- the reference tests' synthetic pattern: tests/convolve.cc:74-84,107-117,140-150
+def ref_pattern(xlen, hlen=50):
+    i = np.arange(xlen, dtype=np.float32)
+    x = (np.sin(i).astype(np.float32) * np.float32(100)).astype(np.float32)
+    h = (np.arange(hlen, dtype=np.float32) / np.float32(hlen - 1.0)).astype(np.float32)
+    return x, h
+
+for op in ("convolve", "correlate"):
+    x, h = ref_pattern(1020); add(f"sin1020_{op}_fft", x, h, op, "fft")
+    add(f"sin1020_{op}_simd0", x, h, op, "simd0")
+    x, h = ref_pattern(1021); add(f"sin1021_{op}_os", x, h, op, "overlap_save")
+    add(f"sin1021_{op}_simd0", x, h, op, "simd0")
+    x, h = ref_pattern(1024); add(f"sin1024_{op}_simd1", x, h, op, "simd1")
+    add(f"sin1024_{op}_simd0", x, h, op, "simd0")
+
+# --- BASELINE configs that fit a fixture (U(-1,1), seed 0xC0FFEE + config index)
+def uni(seed, n):
+    return np.random.default_rng(seed).uniform(-1, 1, n).astype(np.float32)
+
+x, h = uni(0xC0FFEE + 1, 1024), uni(0xC1FFEE + 1, 50)
+add("c1_convolve_auto", x, h, "convolve", "auto")
+add("c1_convolve_simd1", x, h, "convolve", "simd1")
+add("c1_convolve_simd0", x, h, "convolve", "simd0")
+x, h = uni(0xC0FFEE + 2, 65536), uni(0xC1FFEE + 2, 512)
+add("c2_correlate_auto", x, h, "correlate", "auto")
+add("c2_correlate_simd0", x, h, "correlate", "simd0")
+x, h = uni(0xC0FFEE + 3, 16384), uni(0xC1FFEE + 3, 64)
+add("c3_signal_convolve_auto", x, h, "convolve", "auto")
+add("c3_signal_convolve_simd0", x, h, "convolve", "simd0")
+
+# --- edge shapes and selector boundaries (src/convolve.c:349-363)
+for (xl, hl) in [(1, 1), (8, 1), (7, 7), (64, 64), (200, 50), (201, 50), (350, 350),
+                 (351, 350), (512, 512), (37, 5), (1000, 3), (4099, 129)]:
+    x, h = uni(1000 + xl, xl), uni(2000 + hl, hl)
+    for op in ("convolve", "correlate"):
+        add(f"edge_{xl}x{hl}_{op}_auto", x, h, op, "auto", guard=4096)
+        add(f"edge_{xl}x{hl}_{op}_simd0", x, h, op, "simd0")
+# Q1 shape: selector sends (300,128) to overlap-save, first block over-reads x.
+x, h = uni(77, 300), uni(78, 128)
+add("q1_300x128_convolve_auto", x, h, "convolve", "auto", guard=4096)
+add("q1_300x128_convolve_simd0", x, h, "convolve", "simd0")
+
+out = {}
+index = []
+for name, c in cases.items():
+    out[name + "/x"] = c["x"]; out[name + "/h"] = c["h"]; out[name + "/y"] = c["y"]
+    info = c["info"] or {}
+    index.append("|".join([name, c["op"], c["path"], str(info.get("algorithm", -1)),
+                           str(info.get("L", info.get("M", 0)))]))
+out["index"] = np.array(index)
+dst = os.path.join(os.path.dirname(HERE), "tests", "golden", "golden.npz")
+np.savez_compressed(dst, **out)
+print(f"wrote {dst}: {len(cases)} cases, {os.path.getsize(dst)/1e6:.2f} MB")
