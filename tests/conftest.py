@@ -1,0 +1,69 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def _cuda_ok():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def pytest_collection_modifyitems(config, items):
+    if _cuda_ok():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device in this container")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from _oracle import Oracle
+    return Oracle()
+
+
+@pytest.fixture(scope="session")
+def reference():
+    from _oracle import Reference, have_reference
+    if not have_reference():
+        pytest.skip("oracle/_ref/libSimd_ref.so not built (needs /root/reference)")
+    return Reference()
+
+
+@pytest.fixture(scope="session")
+def golden():
+    import numpy as np
+    z = np.load(os.path.join(ROOT, "tests", "golden", "golden.npz"))
+    cases = {}
+    for line in z["index"]:
+        name, op, path, alg, tl = str(line).split("|")
+        cases[name] = dict(x=z[name + "/x"], h=z[name + "/h"], y=z[name + "/y"], op=op,
+                           path=path, algorithm=int(alg), transform=int(tl))
+    return cases
+
+
+@pytest.fixture(scope="session")
+def simd():
+    """The product library through its Python binding (C-ABI underneath)."""
+    import veles.simd_b200 as v
+    return v
+
+
+@pytest.fixture(scope="session")
+def reference_or_none():
+    from _oracle import Reference, have_reference
+    return Reference() if have_reference() else None

@@ -1,0 +1,280 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI (ctypes -> libSimd.so), against
+the CPU oracle, the committed golden fixtures (reference outputs) and size-independent
+properties at the BASELINE.json sizes.
+
+Tolerance (BASELINE.json north_star): rel-L2 <= 1e-5 and max|err| <= 1e-4*||h||_1*max|x|.
+"""
+import numpy as np
+import pytest
+
+from _oracle import parity_ok, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+KAT_X = np.arange(1, 9, dtype=np.float32)
+KAT_H = np.array([10, 9, 8, 7], dtype=np.float32)
+KAT_CONV = [10, 29, 56, 90, 124, 158, 192, 226, 170, 113, 56]
+KAT_CORR = [7, 22, 46, 80, 114, 148, 182, 216, 187, 142, 80]
+
+
+def uni(seed, *shape):
+    return np.random.default_rng(seed).uniform(-1, 1, shape).astype(np.float32)
+
+
+def check(got, want, x, h, what=""):
+    ok, r, m = parity_ok(got, want, x, h)
+    assert ok, f"{what}: rel_l2={r:.3e} max_abs={m:.3e}"
+    return r
+
+
+def test_known_answers_every_entry_point(simd):
+    """tests/convolve.cc:53-71 and tests/correlate.cc:53-71 through all call families."""
+    for corr, want in ((False, KAT_CONV), (True, KAT_CORR)):
+        for s in (0, 1):
+            assert np.allclose(simd.convolve_simd(KAT_X, KAT_H, correlate=corr, simd=s), want, atol=1e-4)
+        for kind in ("", "_fft"):
+            with simd.Handle(8, 4, kind, corr) as hd:
+                assert np.allclose(hd(KAT_X, KAT_H), want, atol=1e-4), (kind, corr)
+    # overlap-save needs h < x/2 (src/convolve.c:105)
+    x = np.concatenate([KAT_X, np.zeros(8, np.float32)])
+    for corr, want in ((False, KAT_CONV), (True, KAT_CORR)):
+        with simd.Handle(16, 4, "_overlap_save", corr) as hd:
+            y = hd(x, KAT_H)
+        if corr:
+            assert np.allclose(y[:11], want, atol=1e-4)
+        else:
+            assert np.allclose(y[:11], want, atol=1e-4)
+
+
+def test_golden_fixtures(simd, golden):
+    """Every fixture (outputs of the reference's own code) through the matching entry point."""
+    worst = 0.0
+    for name, c in golden.items():
+        x, h, y = c["x"], c["h"], c["y"]
+        corr = c["op"] == "correlate"
+        if c["path"] in ("simd0", "simd1"):
+            got = simd.convolve_simd(x, h, correlate=corr, simd=int(c["path"][-1]))
+        else:
+            kind = {"fft": "_fft", "overlap_save": "_overlap_save", "auto": ""}[c["path"]]
+            with simd.Handle(x.size, h.size, kind, corr) as hd:
+                got = hd(x, h)
+                if kind == "":
+                    assert hd.algorithm == simd.select_algorithm(x.size, h.size)
+        worst = max(worst, check(got, y, x, h, name))
+    assert worst < 1e-5
+
+
+def test_reference_test_shapes(simd, golden):
+    """tests/convolve.cc:73-166 / tests/correlate.cc:73-152 with their own criteria."""
+    for op in ("convolve", "correlate"):
+        corr = op == "correlate"
+        for xl, kind in ((1020, "_fft"), (1021, "_overlap_save"), (1024, None)):
+            c = golden[f"sin{xl}_{op}_simd0"]
+            if kind is None:
+                got = simd.convolve_simd(c["x"], c["h"], correlate=corr)
+            else:
+                with simd.Handle(xl, 50, kind, corr) as hd:
+                    got = hd(c["x"], c["h"])
+            # sinf(i)*100 inputs: outputs ~1e3, float32 ulp there ~6e-5
+            assert np.max((got - c["y"]) ** 2) <= 1e-6 or np.max(np.abs(got - c["y"])) <= 1e-3
+
+
+@pytest.mark.parametrize("xl,hl", [(1, 1), (2, 1), (1, 7), (7, 7), (33, 5), (100, 100), (257, 17),
+                                   (2049, 16), (2048, 48), (5000, 63), (4097, 129), (70000, 64),
+                                   (3000, 1500)])
+def test_direct_kernel_shapes(simd, oracle, xl, hl):
+    x, h = uni(xl, xl), uni(hl + 7, hl)
+    for corr in (False, True):
+        got = simd.convolve_simd(x, h, correlate=corr)
+        check(got, oracle.convolve_f64(x, h, corr), x, h, f"direct {xl}x{hl} corr={corr}")
+
+
+@pytest.mark.parametrize("xl,hl", [(16, 4), (201, 50), (300, 128), (1021, 50), (4099, 129), (9000, 512),
+                                   (65536, 512), (20000, 1000), (50000, 2048), (100000, 4096),
+                                   (70000, 8192), (100000, 20000), (40000, 12000)])
+def test_overlap_save_shapes(simd, oracle, xl, hl):
+    """convolve_overlap_save over every transform length, incl. partitioned impulse
+    responses (h > 8192) and SURVEY Q1 (300,128): samples past x are zeros."""
+    x, h = uni(xl + 1, xl), uni(hl + 2, hl)
+    for corr in (False, True):
+        with simd.Handle(xl, hl, "_overlap_save", corr) as hd:
+            assert hd.reverse == int(corr)
+            L = hd.transform_length
+            assert 256 <= L <= 16384
+            got = hd(x, h)
+        want = oracle.convolve_fft(x, h, corr) if hl > 3000 else oracle.convolve_f64(x, h, corr)
+        check(got, want, x, h, f"os {xl}x{hl} L={L} corr={corr}")
+
+
+@pytest.mark.parametrize("xl,hl", [(8, 4), (351, 350), (512, 512), (1020, 50), (5000, 3000),
+                                   (9000, 7000), (30000, 30000), (100, 900), (20000, 1000)])
+def test_fft_shapes_and_handle_reuse(simd, oracle, xl, hl):
+    """convolve_fft: whole-signal transform when x+h-1 <= 16384, partitioned beyond.  The
+    handle is reusable (the reference's is single-use)."""
+    x, h = uni(xl + 3, xl), uni(hl + 4, hl)
+    for corr in (False, True):
+        want = oracle.convolve_fft(x, h, corr)
+        with simd.Handle(xl, hl, "_fft", corr) as hd:
+            M = hd.transform_length
+            assert M >= xl + hl - 1 and M & (M - 1) == 0 and M < 2 * (xl + hl - 1)
+            for call in range(3):
+                check(hd(x, h), want, x, h, f"fft {xl}x{hl} call {call} corr={corr}")
+
+
+def test_best_method_handle_matches_every_algorithm(simd, oracle):
+    for xl, hl in [(1024, 50), (65536, 512), (16384, 64), (6000, 5000), (40000, 300)]:
+        x, h = uni(xl, xl), uni(hl, hl)
+        want = oracle.convolve_f64(x, h)
+        with simd.Handle(xl, hl) as hd:
+            assert (hd.handle.x_length, hd.handle.h_length) == (xl, hl)
+            check(hd(x, h), want, x, h, f"auto {xl}x{hl} alg={hd.algorithm}")
+        check(simd.convolve_simd(x, h), want, x, h, "direct")
+        if hl < xl // 2:
+            with simd.Handle(xl, hl, "_overlap_save") as hd:
+                check(hd(x, h), want, x, h, "os")
+        with simd.Handle(xl, hl, "_fft") as hd:
+            check(hd(x, h), want, x, h, "fft")
+
+
+def test_device_pointers_match_host_pointers(simd):
+    import torch
+    simd.use_torch_stream()
+    for xl, hl in [(1024, 50), (65536, 512), (6000, 5000)]:
+        x, h = uni(xl, xl), uni(hl, hl)
+        xd, hd_ = torch.from_numpy(x).cuda(), torch.from_numpy(h).cuda()
+        for corr in (False, True):
+            with simd.Handle(xl, hl, "", corr) as hd:
+                host = hd(x, h)
+                dev = hd(xd, hd_)
+                torch.cuda.synchronize()
+                assert np.array_equal(dev.cpu().numpy(), host)
+            d2 = simd.convolve_simd(xd, hd_, correlate=corr)
+            torch.cuda.synchronize()
+            assert np.array_equal(d2.cpu().numpy(), simd.convolve_simd(x, h, correlate=corr))
+
+
+def test_linearity_and_shift(simd):
+    """Properties that hold at any size: conv(a*x1 + x2) = a*conv(x1) + conv(x2); delaying x
+    delays the output."""
+    xl, hl = 50000, 700
+    x1, x2, h = uni(1, xl), uni(2, xl), uni(3, hl)
+    with simd.Handle(xl, hl) as hd:
+        y1, y2 = hd(x1, h), hd(x2, h)
+        y3 = hd((2.5 * x1 + x2).astype(np.float32), h)
+    assert rel_l2(y3, 2.5 * y1 + y2) < 5e-6
+    xs = np.concatenate([np.zeros(123, np.float32), x1[:-123]])
+    with simd.Handle(xl, hl) as hd:
+        ys = hd(xs, h)
+    # outputs that do not see the 123 samples pushed off the end of x
+    assert rel_l2(ys[123:xl], y1[:xl - 123]) < 5e-6
+
+
+def test_batch_c3_shape(simd, oracle):
+    """BASELINE config 3 at full size: 4096 signals x 16384, h = 64 (direct-kernel regime)."""
+    import torch
+    simd.use_torch_stream()
+    B, xl, hl = 4096, 16384, 64
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + 3)
+    x = torch.rand((B, xl), generator=g, device="cuda") * 2 - 1
+    h = torch.rand((hl,), generator=g, device="cuda") * 2 - 1
+    with simd.Handle(xl, hl) as hd:
+        assert hd.algorithm == simd.ALG_BRUTE_FORCE
+        y = hd(x, h)
+        torch.cuda.synchronize()
+    assert y.shape == (B, xl + hl - 1)
+    hn = h.cpu().numpy()
+    for b in (0, 1, 777, 2048, 4095):
+        xb = x[b].cpu().numpy()
+        check(y[b].cpu().numpy(), oracle.convolve_brute(xb, hn), xb, hn, f"c3 row {b}")
+    # sum of a full convolution = (sum x)(sum h), every row (catches any missing tile)
+    lhs = y.double().sum(dim=1)
+    rhs = x.double().sum(dim=1) * h.double().sum()
+    assert torch.max(torch.abs(lhs - rhs)).item() < 1e-2
+    # same batch through the correlate entry point equals convolution with flipped h
+    with simd.Handle(xl, hl, "", True) as hd:
+        yc = hd(x[:64].contiguous(), torch.flip(h, [0]).contiguous())
+        torch.cuda.synchronize()
+    assert torch.equal(yc, y[:64])
+
+
+def test_batch_c4_shape(simd, oracle, reference_or_none):
+    """BASELINE config 4 at full size: 1024 signals x 262144, h = 4096 (overlap-save)."""
+    import torch
+    simd.use_torch_stream()
+    B, xl, hl = 1024, 262144, 4096
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + 4)
+    x = torch.rand((B, xl), generator=g, device="cuda") * 2 - 1
+    h = torch.rand((hl,), generator=g, device="cuda") * 2 - 1
+    with simd.Handle(xl, hl) as hd:
+        assert hd.algorithm == simd.ALG_OVERLAP_SAVE
+        y = hd(x, h)
+        torch.cuda.synchronize()
+    hn = h.cpu().numpy()
+    for b in (0, 511, 1023):
+        xb = x[b].cpu().numpy()
+        want = oracle.convolve_overlap_save(xb, hn)       # reference algorithm, L = 16384
+        check(y[b].cpu().numpy(), want, xb, hn, f"c4 row {b}")
+        if reference_or_none is not None and b == 0:
+            check(y[b].cpu().numpy(), reference_or_none.handle_call("", xb, hn), xb, hn, "c4 vs _ref")
+    lhs = y.double().sum(dim=1)
+    rhs = x.double().sum(dim=1) * h.double().sum()
+    assert torch.max(torch.abs(lhs - rhs) / (1 + torch.abs(rhs))).item() < 1e-3
+    del y, x
+    torch.cuda.empty_cache()
+
+
+def test_long_signal_c5_shape(simd, oracle):
+    """BASELINE config 5 at full size: x = 2^30 samples, h = 8192, on one GPU.  Windows of
+    the result are checked against a float64 direct convolution of the matching x window."""
+    import torch
+    simd.use_torch_stream()
+    xl, hl = 2 ** 30, 8192
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + 5)
+    x = torch.rand((xl,), generator=g, device="cuda") * 2 - 1
+    h = torch.rand((hl,), generator=g, device="cuda") * 2 - 1
+    with simd.Handle(xl, hl) as hd:
+        assert hd.algorithm == simd.ALG_OVERLAP_SAVE
+        L = hd.transform_length
+        y = hd(x, h)
+        torch.cuda.synchronize()
+    step = L - hl + 1
+    hn = h.cpu().numpy()
+    W = 3000
+    starts = [0, step - 1500, 7 * step - 10, xl // 2 + 12345, xl - 1500, xl + hl - 1 - W]
+    for n0 in starts:
+        lo = max(0, n0 - (hl - 1))
+        hi = min(xl, n0 + W)
+        xw = x[lo:hi].cpu().numpy()
+        full = oracle.convolve_f64(xw, hn)             # index k <-> output lo + k
+        want = full[n0 - lo:n0 - lo + W]
+        got = y[n0:n0 + W].cpu().numpy()
+        # windows at the far end include the tail where x has run out: pad is implicit
+        ok, r, m = parity_ok(got, want[:got.size], xw, hn)
+        assert ok, (n0, r, m)
+    total = y.double().sum().item()
+    want_total = x.double().sum().item() * h.double().sum().item()
+    assert abs(total - want_total) <= 1e-6 * (abs(want_total) + xl ** 0.5 * hl ** 0.5)
+    del y, x
+    torch.cuda.empty_cache()
+
+
+def test_filter_shard_reassembles_long_signal(simd, oracle):
+    """Multi-GPU partitioning primitive on one GPU: two shards with an (h-1) halo equal the
+    whole."""
+    xl, hl = 300000, 1000
+    x, h = uni(5, xl), uni(6, hl)
+    want = oracle.convolve_fft(x, h, 0)
+    cut = 150000
+    first = simd.filter_shard(x[:cut], h, 0, hl - 1, cut)
+    second = simd.filter_shard(x[cut - (hl - 1):], h, 0, 0, xl + hl - 1 - cut)
+    got = np.concatenate([first, second])
+    check(got, want, x, h, "two shards")
+    # forced direct kernel on a shard gives the same numbers to rounding
+    d = simd.filter_shard(x[cut - (hl - 1):], h, 0, 0, 5000, algorithm=0)
+    assert rel_l2(d, second[:5000]) < 5e-6
+
+
+def test_kernel_launch_counter(simd):
+    before = simd.lib.simd_b200_kernel_launches()
+    simd.convolve_simd(KAT_X, KAT_H)
+    assert simd.lib.simd_b200_kernel_launches() == before + 1

@@ -1,0 +1,297 @@
+"""veles.simd_b200 -- Python face of libSimd.so (B200 build of the veles.simd convolve /
+cross-correlate hot path).
+
+This module is a thin ctypes binding over the C-ABI library built from src/*.c and
+csrc/*.cu; it exists for tests, the benchmark and Python callers.  The product is the
+shared library: C callers link it directly through include/simd/*.h.
+
+There is NO CPU fallback.  Importing works anywhere (so that host-side logic such as the
+selector can be exercised without a GPU), but every compute call goes to the CUDA kernels
+and aborts the process with a message if no CUDA device is usable; a missing libSimd.so
+raises ImportError at import time.
+
+Names mirror the reference API (/root/reference/inc/simd/convolve.h, correlate.h):
+    lib.convolve_simd, lib.convolve_initialize, ...   raw ctypes functions
+    convolve(x, h), cross_correlate(x, h)             numpy / torch convenience wrappers
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libSimd.so")
+
+_fp = C.POINTER(C.c_float)
+
+ALG_BRUTE_FORCE, ALG_FFT, ALG_OVERLAP_SAVE = 0, 1, 2
+
+
+class ConvolutionOverlapSaveHandle(C.Structure):
+    """include/simd/convolve_structs.h (reference: convolve_structs.h:39-48)."""
+    _fields_ = [("fft_plan", C.c_void_p), ("fft_inverse_plan", C.c_void_p),
+                ("fft_boiler_plate", C.c_void_p), ("H", C.c_void_p),
+                ("x_length", C.c_size_t), ("h_length", C.c_size_t),
+                ("L", C.POINTER(C.c_int)), ("reverse", C.c_int)]
+
+
+class ConvolutionFFTHandle(C.Structure):
+    """include/simd/convolve_structs.h (reference: convolve_structs.h:50-58)."""
+    _fields_ = [("fft_plan", C.c_void_p), ("fft_inverse_plan", C.c_void_p),
+                ("M", C.POINTER(C.c_int)), ("x_length", C.c_int), ("h_length", C.c_int),
+                ("inputs", C.c_void_p), ("reverse", C.c_int)]
+
+
+class _HandleUnion(C.Union):
+    _fields_ = [("fft", ConvolutionFFTHandle), ("os", ConvolutionOverlapSaveHandle)]
+
+
+class ConvolutionHandle(C.Structure):
+    """include/simd/convolve_structs.h (reference: convolve_structs.h:66-74)."""
+    _fields_ = [("algorithm", C.c_int), ("x_length", C.c_int), ("h_length", C.c_int),
+                ("handle", _HandleUnion)]
+
+
+def build(verbose=False):
+    """Compile libSimd.so in-tree (nvcc -gencode arch=compute_100a,code=sm_100a)."""
+    subprocess.run(["make", "-C", _HERE, "--no-print-directory"] + ([] if verbose else ["-s"]),
+                   check=True)
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `make -C {_HERE}` "
+            "(or __graft_entry__.build()); veles.simd_b200 has no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    sz, vp = C.c_size_t, C.c_void_p
+    for p in ("convolve", "cross_correlate"):
+        f = getattr(L, p + "_simd")
+        f.argtypes = [C.c_int, vp, sz, vp, sz, vp]
+        f.restype = None
+        for kind, H in (("_fft", ConvolutionFFTHandle),
+                        ("_overlap_save", ConvolutionOverlapSaveHandle),
+                        ("", ConvolutionHandle)):
+            ini = getattr(L, p + kind + "_initialize")
+            ini.argtypes = [sz, sz]
+            ini.restype = H
+            run = getattr(L, p + kind)
+            run.argtypes = [H, vp, vp, vp]
+            run.restype = None
+            fin = getattr(L, p + kind + "_finalize")
+            fin.argtypes = [H]
+            fin.restype = None
+        b = getattr(L, p + "_batch")
+        b.argtypes = [ConvolutionHandle, vp, sz, vp, vp, sz, sz]
+        b.restype = None
+    L.simd_b200_filter_shard.argtypes = [vp, sz, vp, sz, C.c_int, sz, vp, sz, C.c_int]
+    L.simd_b200_filter_shard.restype = None
+    L.simd_b200_select_algorithm.argtypes = [sz, sz]
+    L.simd_b200_select_algorithm.restype = C.c_int
+    L.simd_b200_transform_length.argtypes = [sz, sz]
+    L.simd_b200_transform_length.restype = C.c_int
+    L.simd_b200_set_stream.argtypes = [vp]
+    L.simd_b200_set_stream.restype = None
+    L.simd_b200_get_stream.restype = vp
+    L.simd_b200_synchronize.restype = None
+    L.simd_b200_device_count.restype = C.c_int
+    L.simd_b200_kernel_launches.restype = C.c_longlong
+    L.simd_b200_profile.argtypes = [C.c_int]
+    L.simd_b200_profile.restype = None
+    L.simd_b200_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
+    L.simd_b200_profile_collect.restype = None
+    L.mallocf.argtypes = [sz]
+    L.mallocf.restype = vp
+    L.malloc_aligned.argtypes = [sz]
+    L.malloc_aligned.restype = vp
+    L.memsetf.argtypes = [vp, C.c_float, sz]
+    L.memsetf.restype = None
+    L.rmemcpyf.argtypes = [vp, vp, sz]
+    L.rmemcpyf.restype = vp
+    return L
+
+
+lib = _load()
+
+#: every symbol include/simd/*.h declares (checked by tests/test_abi.py)
+EXPORTED_SYMBOLS = (
+    "convolve_simd convolve_overlap_save_initialize convolve_overlap_save "
+    "convolve_overlap_save_finalize convolve_fft_initialize convolve_fft convolve_fft_finalize "
+    "convolve_initialize convolve convolve_finalize cross_correlate_simd "
+    "cross_correlate_fft_initialize cross_correlate_fft cross_correlate_fft_finalize "
+    "cross_correlate_overlap_save_initialize cross_correlate_overlap_save "
+    "cross_correlate_overlap_save_finalize cross_correlate_initialize cross_correlate "
+    "cross_correlate_finalize mallocf malloc_aligned memsetf rmemcpyf convolve_batch "
+    "cross_correlate_batch simd_b200_filter_shard simd_b200_select_algorithm "
+    "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
+    "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
+    "simd_b200_profile simd_b200_profile_collect").split()
+
+
+def _is_torch(a):
+    return type(a).__module__.startswith("torch")
+
+
+def _ptr(a):
+    """Raw address of a numpy array (host) or torch tensor (host or device)."""
+    if _is_torch(a):
+        assert a.dtype.is_floating_point and a.element_size() == 4 and a.is_contiguous()
+        return a.data_ptr()
+    assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data
+
+
+def _empty_like(a, shape):
+    if _is_torch(a):
+        import torch
+        return torch.empty(shape, dtype=torch.float32, device=a.device)
+    return np.empty(shape, dtype=np.float32)
+
+
+def use_torch_stream():
+    """Make the library enqueue on torch's current CUDA stream (so torch.cuda.Event timing
+    and torch allocator stream-ordering see the kernels)."""
+    import torch
+    lib.simd_b200_set_stream(C.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+
+def profile(enable):
+    lib.simd_b200_profile(int(enable))
+
+
+def profile_collect():
+    """{kind: (total_ms, launches)} for kinds direct / fused / spectrum since the last call."""
+    ms = (C.c_double * 3)()
+    cnt = (C.c_longlong * 3)()
+    lib.simd_b200_profile_collect(ms, cnt)
+    return {k: (ms[i], cnt[i]) for i, k in enumerate(("direct", "fused", "spectrum"))}
+
+
+def select_algorithm(x_length, h_length):
+    return lib.simd_b200_select_algorithm(x_length, h_length)
+
+
+def transform_length(x_length, h_length):
+    return lib.simd_b200_transform_length(x_length, h_length)
+
+
+def _prep(x, h):
+    if not _is_torch(x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+    if not _is_torch(h):
+        h = np.ascontiguousarray(h, dtype=np.float32)
+    return x, h
+
+
+def convolve_simd(x, h, correlate=False, simd=1, out=None):
+    """convolve_simd / cross_correlate_simd (direct kernel).  1-D x and h."""
+    x, h = _prep(x, h)
+    n, m = x.shape[-1], h.shape[-1]
+    if out is None:
+        out = _empty_like(x, (n + m - 1,))
+    fn = lib.cross_correlate_simd if correlate else lib.convolve_simd
+    fn(int(simd), _ptr(x), n, _ptr(h), m, _ptr(out))
+    return out
+
+
+class Handle:
+    """RAII wrapper over the three handle families.
+    kind: "" (best method), "_fft", "_overlap_save"; correlate selects cross_correlate_*."""
+
+    def __init__(self, x_length, h_length, kind="", correlate=False):
+        self.kind, self.correlate = kind, correlate
+        self.prefix = "cross_correlate" if correlate else "convolve"
+        self.x_length, self.h_length = int(x_length), int(h_length)
+        self.handle = getattr(lib, self.prefix + kind + "_initialize")(self.x_length, self.h_length)
+        self._open = True
+
+    @property
+    def algorithm(self):
+        if self.kind == "":
+            return self.handle.algorithm
+        return ALG_FFT if self.kind == "_fft" else ALG_OVERLAP_SAVE
+
+    @property
+    def transform_length(self):
+        """L (overlap-save) or M (FFT) as the handle reports it; None for brute force."""
+        if self.kind == "_fft":
+            return self.handle.M[0]
+        if self.kind == "_overlap_save":
+            return self.handle.L[0]
+        if self.handle.algorithm == ALG_FFT:
+            return self.handle.handle.fft.M[0]
+        if self.handle.algorithm == ALG_OVERLAP_SAVE:
+            return self.handle.handle.os.L[0]
+        return None
+
+    @property
+    def reverse(self):
+        if self.kind != "":
+            return self.handle.reverse
+        if self.handle.algorithm == ALG_FFT:
+            return self.handle.handle.fft.reverse
+        if self.handle.algorithm == ALG_OVERLAP_SAVE:
+            return self.handle.handle.os.reverse
+        return None
+
+    def __call__(self, x, h, out=None):
+        """One signal (1-D x) through <prefix><kind>(), or a batch (2-D x, best-method
+        handles only) through <prefix>_batch()."""
+        x, h = _prep(x, h)
+        assert x.shape[-1] == self.x_length and h.shape[-1] == self.h_length
+        olen = self.x_length + self.h_length - 1
+        if x.ndim == 1:
+            if out is None:
+                out = _empty_like(x, (olen,))
+            getattr(lib, self.prefix + self.kind)(self.handle, _ptr(x), _ptr(h), _ptr(out))
+            return out
+        assert x.ndim == 2 and self.kind == "", "batches go through the best-method handle"
+        if out is None:
+            out = _empty_like(x, (x.shape[0], olen))
+        x_stride = x.stride(0) if _is_torch(x) else x.strides[0] // 4
+        o_stride = out.stride(0) if _is_torch(out) else out.strides[0] // 4
+        getattr(lib, self.prefix + "_batch")(self.handle, _ptr(x), x_stride, _ptr(h), _ptr(out),
+                                             o_stride, x.shape[0])
+        return out
+
+    def close(self):
+        if self._open:
+            getattr(lib, self.prefix + self.kind + "_finalize")(self.handle)
+            self._open = False
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def convolve(x, h, correlate=False):
+    """initialize -> run -> finalize through the best-method handle.  x may be 1-D (one
+    signal) or 2-D (a batch of independent signals sharing h)."""
+    with Handle(x.shape[-1], h.shape[-1], "", correlate) as hd:
+        out = hd(x, h)
+        if _is_torch(out) and out.is_cuda:
+            lib.simd_b200_synchronize()
+    return out
+
+
+def cross_correlate(x, h):
+    return convolve(x, h, correlate=True)
+
+
+def filter_shard(x, h, reverse, left_pad, result_length, algorithm=-1, out=None):
+    """simd_b200_filter_shard: result[n] = sum_j g[j] X(n + j - left_pad)."""
+    x, h = _prep(x, h)
+    if out is None:
+        out = _empty_like(x, (result_length,))
+    lib.simd_b200_filter_shard(_ptr(x), x.shape[-1], _ptr(h), h.shape[-1], int(reverse),
+                               int(left_pad), _ptr(out), int(result_length), int(algorithm))
+    return out

@@ -1,0 +1,328 @@
+// context.cu -- device context, plans and the host<->device boundary of libSimd (B200).
+//
+// The reference API takes host float* (inc/simd/convolve.h:57-59,82-85,99-102,119-121).
+// b200_run() classifies every pointer with cudaPointerGetAttributes: host pointers are
+// staged through device buffers (and the call returns with the result in host memory),
+// device / managed pointers are used in place and the work is left asynchronous on the
+// library stream.  There is no CPU fallback: without a usable CUDA device every compute
+// entry point aborts with a message.
+#include "b200_device.cuh"
+#include <atomic>
+#include <mutex>
+#include <string.h>
+#include <vector>
+
+namespace {
+
+constexpr int kMaxDev = 16;
+
+struct Staging {        // grow-only device + pinned-free staging for host-pointer callers
+  float *x = nullptr, *h = nullptr, *out = nullptr;
+  size_t x_cap = 0, h_cap = 0, out_cap = 0;
+};
+
+struct DeviceCtx {
+  cudaStream_t own_stream = nullptr;   // created lazily, non-blocking
+  Staging staging;                     // used by handle-less calls (convolve_simd, ...)
+  float2 *spectrum = nullptr;          // scratch for handle-less FFT jobs
+  size_t spectrum_cap = 0;
+};
+
+std::mutex g_mu;                 // guards contexts, the shared staging and user stream
+DeviceCtx g_ctx[kMaxDev];
+std::atomic<void *> g_user_stream{nullptr};
+std::atomic<int> g_have_user_stream{0};
+std::atomic<long long> g_launches{0};
+
+int current_device() {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) {
+    fprintf(stderr,
+            "libSimd(b200): no usable CUDA device (%s). This library has no CPU fallback.\n",
+            cudaGetErrorString(err));
+    abort();
+  }
+  B200_REQUIRE(dev >= 0 && dev < kMaxDev, "device index out of range");
+  return dev;
+}
+
+cudaStream_t current_stream() {
+  if (g_have_user_stream.load()) return (cudaStream_t)g_user_stream.load();
+  int dev = current_device();
+  std::lock_guard<std::mutex> lock(g_mu);
+  if (!g_ctx[dev].own_stream) {
+    B200_CUDA_CHECK(cudaStreamCreateWithFlags(&g_ctx[dev].own_stream, cudaStreamNonBlocking));
+  }
+  return g_ctx[dev].own_stream;
+}
+
+bool is_device_pointer(const void *p) {
+  cudaPointerAttributes attr;
+  cudaError_t err = cudaPointerGetAttributes(&attr, p);
+  if (err != cudaSuccess) {
+    cudaGetLastError();   // clear; treat as plain host memory
+    return false;
+  }
+  return attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+}
+
+void grow(float **buf, size_t *cap, size_t need) {
+  if (need <= *cap) return;
+  if (*buf) B200_CUDA_CHECK(cudaFree(*buf));
+  size_t n = need + need / 8 + 256;
+  B200_CUDA_CHECK(cudaMalloc(buf, n * sizeof(float)));
+  *cap = n;
+}
+
+}  // namespace
+
+struct B200Plan {
+  int magic;
+  int algorithm;
+  int device;
+  i64 x_len, h_len;
+  OsDevPlan os;
+  Staging staging;
+  std::mutex mu;       // one thread per handle at a time (reference: shared scratch)
+};
+
+void b200_count_launch(int n) { g_launches.fetch_add(n); }
+
+// ---- optional per-kernel event timing -----------------------------------------------------
+namespace {
+std::atomic<int> g_prof_on{0};
+std::mutex g_prof_mu;
+struct ProfPair { cudaEvent_t e0, e1; int kind; };
+std::vector<ProfPair> g_prof_pairs;
+cudaEvent_t g_prof_open[B200_PROF_KINDS];
+}  // namespace
+
+void b200_prof_begin(int kind, cudaStream_t stream) {
+  if (!g_prof_on.load()) return;
+  std::lock_guard<std::mutex> lock(g_prof_mu);
+  B200_CUDA_CHECK(cudaEventCreate(&g_prof_open[kind]));
+  B200_CUDA_CHECK(cudaEventRecord(g_prof_open[kind], stream));
+}
+
+void b200_prof_end(int kind, cudaStream_t stream) {
+  if (!g_prof_on.load()) return;
+  std::lock_guard<std::mutex> lock(g_prof_mu);
+  ProfPair p;
+  p.e0 = g_prof_open[kind];
+  p.kind = kind;
+  B200_CUDA_CHECK(cudaEventCreate(&p.e1));
+  B200_CUDA_CHECK(cudaEventRecord(p.e1, stream));
+  g_prof_pairs.push_back(p);
+}
+
+extern "C" void b200_profile_enable(int on) { g_prof_on.store(on); }
+
+// Waits for the recorded events, adds each kind's elapsed time and launch count to
+// total_ms[kind] / count[kind] (arrays of B200_PROF_KINDS) and clears the record.
+extern "C" void b200_profile_collect(double *total_ms, long long *count) {
+  std::lock_guard<std::mutex> lock(g_prof_mu);
+  for (int k = 0; k < B200_PROF_KINDS; k++) { total_ms[k] = 0; count[k] = 0; }
+  for (ProfPair &p : g_prof_pairs) {
+    B200_CUDA_CHECK(cudaEventSynchronize(p.e1));
+    float ms = 0;
+    B200_CUDA_CHECK(cudaEventElapsedTime(&ms, p.e0, p.e1));
+    total_ms[p.kind] += ms;
+    count[p.kind] += 1;
+    cudaEventDestroy(p.e0);
+    cudaEventDestroy(p.e1);
+  }
+  g_prof_pairs.clear();
+}
+
+extern "C" long long b200_kernel_launches(void) { return g_launches.load(); }
+
+extern "C" void b200_set_stream(void *s) {
+  g_user_stream.store(s);
+  g_have_user_stream.store(1);
+}
+
+extern "C" void *b200_get_stream(void) { return (void *)current_stream(); }
+
+extern "C" void b200_synchronize(void) {
+  B200_CUDA_CHECK(cudaStreamSynchronize(current_stream()));
+}
+
+extern "C" int b200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len,
+                                      int n_fft) {
+  B200Plan *plan = new B200Plan();
+  plan->magic = 0xB200;
+  plan->algorithm = algorithm;
+  plan->device = current_device();
+  plan->x_len = x_len;
+  plan->h_len = h_len;
+  B200_REQUIRE(n_fft >= B200_FFT_MIN && n_fft <= B200_FFT_MAX && (n_fft & (n_fft - 1)) == 0,
+               "transform length must be a power of two in range");
+  plan->os.n_fft = n_fft;
+  // whole-signal transform (FFT algorithm, x+h-1 fits): one partition holds all taps
+  const bool whole = algorithm == B200_ALG_FFT && x_len + h_len - 1 <= n_fft;
+  plan->os.part_taps = whole ? (int)h_len : b200_os_part_taps(n_fft, h_len);
+  plan->os.max_parts = (int)((h_len + plan->os.part_taps - 1) / plan->os.part_taps);
+  plan->os.twiddles = b200_twiddles(n_fft);
+  B200_CUDA_CHECK(cudaMalloc(&plan->os.spectrum,
+                             sizeof(float2) * (size_t)n_fft * plan->os.max_parts));
+  // staging for host-pointer callers is sized now so the call path does not allocate
+  grow(&plan->staging.x, &plan->staging.x_cap, (size_t)x_len);
+  grow(&plan->staging.h, &plan->staging.h_cap, (size_t)h_len);
+  grow(&plan->staging.out, &plan->staging.out_cap, (size_t)(x_len + h_len - 1));
+  return plan;
+}
+
+extern "C" void b200_plan_destroy(B200Plan *plan) {
+  if (!plan) return;
+  B200_REQUIRE(plan->magic == 0xB200, "not a libSimd(b200) plan");
+  int prev = current_device();
+  if (prev != plan->device) B200_CUDA_CHECK(cudaSetDevice(plan->device));
+  // outstanding asynchronous work may still read the spectrum / staging buffers
+  B200_CUDA_CHECK(cudaDeviceSynchronize());
+  cudaFree(plan->os.spectrum);
+  cudaFree(plan->staging.x);
+  cudaFree(plan->staging.h);
+  cudaFree(plan->staging.out);
+  if (prev != plan->device) B200_CUDA_CHECK(cudaSetDevice(prev));
+  plan->magic = 0;
+  delete plan;
+}
+
+extern "C" int b200_plan_n_fft(const B200Plan *plan) { return plan->os.n_fft; }
+extern "C" float *b200_plan_spectrum(const B200Plan *plan) { return (float *)plan->os.spectrum; }
+extern "C" float *b200_plan_scratch(const B200Plan *plan) { return plan->staging.x; }
+
+namespace {
+
+void launch_device_job(B200Plan *plan, int algorithm, const DevJob &dj, cudaStream_t stream) {
+  if (algorithm == B200_ALG_DIRECT) {
+    b200_direct_launch(dj, stream);
+    return;
+  }
+  if (plan) {
+    bool single = algorithm == B200_ALG_FFT && plan->os.max_parts == 1 &&
+                  dj.pad == dj.h_len - 1 && dj.x_len + dj.h_len - 1 <= plan->os.n_fft &&
+                  dj.out_len <= plan->os.n_fft;
+    b200_os_launch(plan->os, dj, single, stream);
+    return;
+  }
+  // handle-less FFT job (extension API with algorithm forced): context-owned scratch
+  int dev = current_device();
+  int n = b200_os_pick_n(dj.h_len, dj.out_len);
+  int taps = b200_os_part_taps(n, dj.h_len);
+  int parts = (int)((dj.h_len + taps - 1) / taps);
+  const float2 *tw = b200_twiddles(n);
+  std::lock_guard<std::mutex> lock(g_mu);
+  DeviceCtx &c = g_ctx[dev];
+  size_t need = (size_t)n * parts;
+  if (need > c.spectrum_cap) {
+    if (c.spectrum) { B200_CUDA_CHECK(cudaDeviceSynchronize()); B200_CUDA_CHECK(cudaFree(c.spectrum)); }
+    B200_CUDA_CHECK(cudaMalloc(&c.spectrum, sizeof(float2) * need));
+    c.spectrum_cap = need;
+  }
+  b200_os_launch_with(tw, c.spectrum, n, taps, dj, false, stream);
+}
+
+}  // namespace
+
+extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
+  B200_REQUIRE(job->x && job->h && job->out, "null pointer argument");
+  B200_REQUIRE(job->x_len > 0 && job->h_len > 0, "zero-length signal");
+  if (plan) B200_REQUIRE(plan->magic == 0xB200, "not a libSimd(b200) plan (stale handle?)");
+  if (job->batch <= 0 || job->out_len <= 0) return;
+  int dev = current_device();
+  if (plan) B200_REQUIRE(plan->device == dev, "handle used on a different device than it was created on");
+  cudaStream_t stream = current_stream();
+
+  const bool xd = is_device_pointer(job->x);
+  const bool hd = is_device_pointer(job->h);
+  const bool od = is_device_pointer(job->out);
+
+  DevJob dj;
+  dj.x = job->x; dj.x_len = job->x_len; dj.x_stride = job->x_stride;
+  dj.h = job->h; dj.h_len = job->h_len;
+  dj.out = job->out; dj.out_len = job->out_len; dj.out_stride = job->out_stride;
+  dj.pad = job->pad; dj.batch = job->batch; dj.reverse = job->reverse;
+
+  if (xd && hd && od) {
+    if (plan) {
+      std::lock_guard<std::mutex> lock(plan->mu);
+      launch_device_job(plan, algorithm, dj, stream);
+    } else {
+      launch_device_job(plan, algorithm, dj, stream);
+    }
+    return;
+  }
+
+  // ---- host-pointer path: stage, run, copy back, synchronise --------------------------
+  std::unique_lock<std::mutex> plan_lock, ctx_lock;
+  Staging *st;
+  if (plan) {
+    plan_lock = std::unique_lock<std::mutex>(plan->mu);
+    st = &plan->staging;
+  } else {
+    // handle-less calls share the per-device staging: serialise them
+    static std::mutex staged_call_mu;
+    ctx_lock = std::unique_lock<std::mutex>(staged_call_mu);
+    st = &g_ctx[dev].staging;
+  }
+  // Batches are processed in chunks so that staging stays bounded and copies overlap
+  // poorly only for the first/last chunk (copy-in of chunk i+1 queues behind compute of i
+  // on the same stream; a second stream would add overlap -- see DESIGN.md).
+  const size_t x_row = (size_t)job->x_len, o_row = (size_t)job->out_len;
+  const size_t budget = (size_t)64 << 20;        // floats per staging buffer (256 MiB)
+  i64 chunk = (i64)(budget / (x_row > o_row ? x_row : o_row));
+  if (chunk < 1) chunk = 1;
+  if (chunk > job->batch) chunk = job->batch;
+  if (!xd) grow(&st->x, &st->x_cap, x_row * (size_t)chunk);
+  if (!hd) grow(&st->h, &st->h_cap, (size_t)job->h_len);
+  if (!od) grow(&st->out, &st->out_cap, o_row * (size_t)chunk);
+
+  if (!hd) {
+    B200_CUDA_CHECK(cudaMemcpyAsync(st->h, job->h, sizeof(float) * job->h_len,
+                                    cudaMemcpyHostToDevice, stream));
+    dj.h = st->h;
+  }
+  for (i64 b0 = 0; b0 < job->batch; b0 += chunk) {
+    const i64 nb = (job->batch - b0) < chunk ? (job->batch - b0) : chunk;
+    dj.batch = nb;
+    if (!xd) {
+      if (nb == 1 || job->x_stride == (i64)x_row) {   // contiguous: no 2-D pitch limit
+        B200_CUDA_CHECK(cudaMemcpyAsync(st->x, job->x + b0 * job->x_stride,
+                                        sizeof(float) * x_row * (size_t)nb,
+                                        cudaMemcpyHostToDevice, stream));
+      } else {
+        B200_CUDA_CHECK(cudaMemcpy2DAsync(st->x, sizeof(float) * x_row,
+                                          job->x + b0 * job->x_stride,
+                                          sizeof(float) * job->x_stride, sizeof(float) * x_row,
+                                          (size_t)nb, cudaMemcpyHostToDevice, stream));
+      }
+      dj.x = st->x; dj.x_stride = (i64)x_row;
+    } else {
+      dj.x = job->x + b0 * job->x_stride;
+    }
+    if (!od) { dj.out = st->out; dj.out_stride = (i64)o_row; }
+    else dj.out = job->out + b0 * job->out_stride;
+    launch_device_job(plan, algorithm, dj, stream);
+    if (!od) {
+      if (nb == 1 || job->out_stride == (i64)o_row) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(job->out + b0 * job->out_stride, st->out,
+                                        sizeof(float) * o_row * (size_t)nb,
+                                        cudaMemcpyDeviceToHost, stream));
+      } else {
+        B200_CUDA_CHECK(cudaMemcpy2DAsync(job->out + b0 * job->out_stride,
+                                          sizeof(float) * job->out_stride, st->out,
+                                          sizeof(float) * o_row, sizeof(float) * o_row,
+                                          (size_t)nb, cudaMemcpyDeviceToHost, stream));
+      }
+    }
+  }
+  B200_CUDA_CHECK(cudaStreamSynchronize(stream));
+}

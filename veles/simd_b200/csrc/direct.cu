@@ -1,0 +1,180 @@
+// direct.cu -- the "brute force" path on the GPU: shared-memory tiled, register-blocked
+// direct convolution / cross-correlation for short impulse responses.
+//
+// Replaces the AVX loops of the reference: convolve_simd (/root/reference/src/convolve.c:
+// 40-101) and cross_correlate_simd (/root/reference/src/correlate.c:74-126).  Both are the
+// same correlation-form sum  out[n] = sum_j g[j] * X(n + j - pad)  with g = reversed h for
+// convolution and g = h for correlation, so one kernel serves both; the reference's
+// per-output beg/end clamps (convolve.c:51-55, correlate.c:80-84) become a zero-filled halo.
+//
+// Layout: a CTA owns TILE = R*TPB consecutive outputs of one signal.  It stages the x window
+// [n0 - pad, n0 - pad + TILE + hc - 1) and the tap block g[c0, c0+hc) in shared memory with
+// coalesced loads, then every thread accumulates R = 16 consecutive outputs in registers,
+// sliding a 32-sample register window over the tile so that each 16-byte shared-memory read
+// feeds 64 FMAs.  The x tile is stored with 4 pad floats per 16 so that the 64-byte-strided
+// float4 reads of a quarter warp hit 8 distinct bank groups.  Results go back through shared
+// memory so the global stores are fully coalesced for any row alignment.
+//
+// Roofline: 2*h_len FLOP and 8 B of HBM traffic per output -> FP32-bound above h_len ~ 45.
+#include "b200_device.cuh"
+
+namespace {
+
+constexpr int kR = 16;          // outputs per thread
+constexpr int kTPB = 128;       // threads per CTA
+constexpr int kTile = kR * kTPB;
+constexpr int kMaxHC = 1024;    // taps staged per pass over the tile
+
+__device__ __forceinline__ int padx(int q) { return q + ((q >> 4) << 2); }
+
+struct DirectParams {
+  const float *x;
+  i64 x_len, x_stride;
+  const float *h;
+  i64 h_len;
+  float *out;
+  i64 out_len, out_stride;
+  i64 pad;
+  i64 tiles_per_signal;
+  int reverse;
+  int hc_max;           // taps per staging pass (multiple of 16)
+};
+
+__global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
+  extern __shared__ float4 smem4[];
+  float *gs = reinterpret_cast<float *>(smem4);          // hc_max + 16 taps
+  float *xs = gs + p.hc_max + 16;                        // padded x window
+
+  const int tid = threadIdx.x;
+  const i64 tile = blockIdx.x;
+  const i64 b = tile / p.tiles_per_signal;
+  const i64 n0 = (tile % p.tiles_per_signal) * kTile;
+  const float *xb = p.x + b * p.x_stride;
+  const i64 remaining = p.out_len - n0;
+  const int cnt = remaining < kTile ? (int)remaining : kTile;
+  const int t0 = tid * kR;
+  // warp-uniform: does any thread of this warp own a live output?
+  const bool active = ((tid & ~31) * kR) < cnt;
+
+  float acc[kR];
+#pragma unroll
+  for (int r = 0; r < kR; r++) acc[r] = 0.f;
+
+  for (i64 c0 = 0; c0 < p.h_len; c0 += p.hc_max) {
+    const int hc = (int)((p.h_len - c0) < p.hc_max ? (p.h_len - c0) : p.hc_max);
+    if (c0 > 0) __syncthreads();
+    // taps of this pass, correlation order
+    for (int j = tid; j < hc; j += kTPB) {
+      i64 gj = c0 + j;
+      gs[j] = p.reverse ? p.h[gj] : p.h[p.h_len - 1 - gj];
+    }
+    // x window of this pass (zero outside the signal)
+    const i64 xi0 = n0 + c0 - p.pad;
+    const int wlen = kTile + hc - 1;
+    if (xi0 >= 0 && xi0 + wlen <= p.x_len) {
+#pragma unroll 8
+      for (int q = tid; q < wlen; q += kTPB) xs[padx(q)] = xb[xi0 + q];
+    } else {
+#pragma unroll 4
+      for (int q = tid; q < wlen; q += kTPB) {
+        i64 i = xi0 + q;
+        xs[padx(q)] = (i >= 0 && i < p.x_len) ? xb[i] : 0.f;
+      }
+    }
+    __syncthreads();
+
+    if (active) {
+      const int hc16 = hc & ~15;
+      float w[32];
+      const float *xrow = xs + padx(t0);     // t0 is a multiple of 16: 20-float rows from here
+      if (hc16 > 0) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          float4 v = *reinterpret_cast<const float4 *>(xrow + 4 * i);
+          w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+        }
+      }
+      for (int j0 = 0; j0 < hc16; j0 += 16) {
+        const float *xn = xrow + ((j0 + 16) >> 4) * 20;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          float4 v = *reinterpret_cast<const float4 *>(xn + 4 * i);
+          w[16 + 4 * i] = v.x; w[17 + 4 * i] = v.y; w[18 + 4 * i] = v.z; w[19 + 4 * i] = v.w;
+        }
+#pragma unroll
+        for (int q4 = 0; q4 < 4; q4++) {
+          float4 g = *reinterpret_cast<const float4 *>(gs + j0 + 4 * q4);
+          const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+          for (int jj = 0; jj < 4; jj++) {
+#pragma unroll
+            for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], w[r + 4 * q4 + jj], acc[r]);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; i++) w[i] = w[i + 16];
+      }
+      // remaining (< 16) taps, four at a time with exact tap predicates
+      for (int j0 = hc16; j0 < hc; j0 += 4) {
+        const int blk = j0 >> 4, off = j0 & 15;    // off in {0,4,8,12}
+        const float *xa = xrow + blk * 20 + off;
+        float wr[20];
+#pragma unroll
+        for (int i = 0; i < 5; i++) {
+          // the 20-sample window may straddle one row boundary
+          int e = off + 4 * i;
+          const float *src = xa + 4 * i + (e >= 16 ? 4 : 0) + (e >= 32 ? 4 : 0);
+          float4 v = *reinterpret_cast<const float4 *>(src);
+          wr[4 * i] = v.x; wr[4 * i + 1] = v.y; wr[4 * i + 2] = v.z; wr[4 * i + 3] = v.w;
+        }
+        float4 g = *reinterpret_cast<const float4 *>(gs + j0);
+        const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+        for (int jj = 0; jj < 4; jj++) {
+          if (j0 + jj < hc) {
+#pragma unroll
+            for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], wr[r + jj], acc[r]);
+          }
+        }
+      }
+    }
+  }
+
+  // results -> shared (same padded rows) -> coalesced global stores
+  __syncthreads();
+  if (active) {
+    float *orow = xs + padx(t0);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      *reinterpret_cast<float4 *>(orow + 4 * i) =
+          make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
+    }
+  }
+  __syncthreads();
+  float *ob = p.out + b * p.out_stride + n0;
+#pragma unroll 4
+  for (int i = tid; i < cnt; i += kTPB) ob[i] = xs[padx(i)];
+}
+
+}  // namespace
+
+void b200_direct_launch(const DevJob &job, cudaStream_t stream) {
+  if (job.batch <= 0 || job.out_len <= 0) return;
+  DirectParams p;
+  p.x = job.x; p.x_len = job.x_len; p.x_stride = job.x_stride;
+  p.h = job.h; p.h_len = job.h_len;
+  p.out = job.out; p.out_len = job.out_len; p.out_stride = job.out_stride;
+  p.pad = job.pad; p.reverse = job.reverse;
+  p.tiles_per_signal = (job.out_len + kTile - 1) / kTile;
+  i64 hc = job.h_len < kMaxHC ? job.h_len : kMaxHC;
+  p.hc_max = (int)((hc + 15) & ~15LL);
+  i64 tiles = p.tiles_per_signal * job.batch;
+  B200_REQUIRE(tiles < 2147483647LL, "direct kernel grid too large");
+  // taps (+16 slack for the float4 tail read) + padded x window (+ two slack rows)
+  size_t smem = sizeof(float) * (size_t)(p.hc_max + 16 + ((kTile + p.hc_max + 32) / 16 + 1) * 20);
+  b200_prof_begin(B200_PROF_DIRECT, stream);
+  direct_kernel<<<(unsigned)tiles, kTPB, smem, stream>>>(p);
+  b200_prof_end(B200_PROF_DIRECT, stream);
+  B200_CUDA_CHECK(cudaGetLastError());
+  b200_count_launch(1);
+}

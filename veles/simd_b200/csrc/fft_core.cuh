@@ -1,0 +1,424 @@
+// fft_core.cuh -- in-register / shared-memory FFT building blocks for the fused
+// overlap-save kernel (os_fft.cu).  Replaces the FFTF calls of the reference
+// (/root/reference/src/convolve.c:131-143,175,198,216) with a hand-written transform whose
+// spectrum never leaves the SM.
+//
+// Everything here is __host__ __device__ and takes the thread index as an argument so that
+// tests/emul/emul_os.cpp can execute the very same index / twiddle logic on the CPU
+// (one loop iteration per CUDA thread, one loop nest per barrier interval).
+//
+// Transform structure for a complex length N = R1*R2*R3 (R2 may be 1):
+//   forward  : decimation in frequency.  A pass over sub-blocks of length NB with radix R
+//              and stride S = NB/R does an R-point DFT over the strided index, applies the
+//              twiddle W_NB^(n''*k) and writes the results back to the positions they were
+//              read from.  After the last pass (S = 1) bin k1 + R1*k2 + R1*R2*k3 sits at
+//              position k1*N/R1 + k2*R3 + k3 ("digit-reversed").
+//   inverse  : the same passes in the opposite order with conjugated twiddles applied before
+//              the butterfly (decimation in time): digit-reversed in, natural order out.
+//   Forward-last and inverse-first work on the same R3 contiguous elements, so the pointwise
+//   product with the filter spectrum happens in registers between them, and the filter
+//   spectrum is stored in exactly the register order of that pass (no reordering pass
+//   anywhere; 1/N is folded into it).
+//
+// Two real segments are transformed at once as z = a + i*b: filtering is linear with a real
+// impulse response, so IFFT(FFT(z) * H) = (a (*) h) + i*(b (*) h) and no Hermitian
+// untangling step is needed (the reference runs one real FFT pair per segment,
+// src/convolve.c:198-216).
+//
+// Shared-memory layout: float2 per complex sample, logical position p stored at
+// p + (p >> 4) (one pad slot per 16) which keeps every pass's half-warp accesses on 16
+// distinct 8-byte bank pairs.
+#pragma once
+
+#include <type_traits>
+
+#if defined(__CUDACC__)
+#define FC_HD __host__ __device__ __forceinline__
+#else
+#define FC_HD inline __attribute__((always_inline))
+#ifndef FC_HOST_FLOAT2
+#define FC_HOST_FLOAT2
+struct float2 { float x, y; };
+static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b; return r; }
+#endif
+#endif
+
+namespace fc {
+
+typedef long long i64;
+
+template <int I, int END, class F>
+FC_HD void static_for(F &&f) {
+  if constexpr (I < END) {
+    f(std::integral_constant<int, I>{});
+    static_for<I + 1, END>(f);
+  }
+}
+
+FC_HD constexpr int pad_pos(int p) { return p + (p >> 4); }
+constexpr int padded_len(int n) { return n + (n >> 4); }
+
+// cos(2*pi*k/32) for k in [0,8]; other octants by symmetry.
+FC_HD constexpr float cos32_tab(int k) {
+  return k == 0 ? 1.0f : k == 1 ? 0.98078528040323044913f : k == 2 ? 0.92387953251128675613f
+       : k == 3 ? 0.83146961230254523708f : k == 4 ? 0.70710678118654752440f
+       : k == 5 ? 0.55557023301960222474f : k == 6 ? 0.38268343236508977173f
+       : k == 7 ? 0.19509032201612826785f : 0.0f;
+}
+FC_HD constexpr float cos32(int k) { return k <= 8 ? cos32_tab(k) : -cos32_tab(16 - k); }  // k in [0,16]
+FC_HD constexpr float sin32(int k) { return k <= 8 ? cos32_tab(8 - k) : cos32_tab(k - 8); }
+
+FC_HD constexpr int bitrev(int v, int bits) {
+  int r = 0;
+  for (int i = 0; i < bits; i++) r |= ((v >> i) & 1) << (bits - 1 - i);
+  return r;
+}
+FC_HD constexpr int ilog2(int v) { int l = 0; while ((1 << l) < v) l++; return l; }
+FC_HD constexpr int hibit(int v) { int h = 1; while (h * 2 <= v) h *= 2; return h; }
+
+FC_HD float2 cmul(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+FC_HD float2 cmul_conj(float2 a, float2 b) {   // a * conj(b)
+  return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
+}
+
+// One radix-2 DIT butterfly with compile-time twiddle w = W_32^K32 (forward:
+// exp(-i*2*pi*K32/32); inverse: its conjugate).
+//   a' = a + w*b ;  b' = a - w*b = 2a - a'      (6 FMA-class operations)
+template <int K32, bool INV>
+FC_HD void bfly(float2 &a, float2 &b) {
+  if constexpr (K32 == 0) {
+    float2 t = b;
+    b = make_float2(a.x - t.x, a.y - t.y);
+    a = make_float2(a.x + t.x, a.y + t.y);
+  } else if constexpr (K32 == 8) {
+    // forward w = -i : w*b = (b.y, -b.x);  inverse w = +i : w*b = (-b.y, b.x)
+    float2 t = INV ? make_float2(-b.y, b.x) : make_float2(b.y, -b.x);
+    b = make_float2(a.x - t.x, a.y - t.y);
+    a = make_float2(a.x + t.x, a.y + t.y);
+  } else {
+    constexpr float wr = cos32(K32);
+    constexpr float wi = INV ? sin32(K32) : -sin32(K32);
+    float nr = a.x + b.x * wr;
+    nr = nr - b.y * wi;
+    float ni = a.y + b.x * wi;
+    ni = ni + b.y * wr;
+    b = make_float2(2.0f * a.x - nr, 2.0f * a.y - ni);
+    a = make_float2(nr, ni);
+  }
+}
+
+// R-point DFT in registers, R in {2,4,8,16,32}.  Decimation in time: input element r must
+// sit in v[bitrev(r)], output bin k is produced in v[k].  INV -> un-normalised inverse.
+template <int R, bool INV>
+FC_HD void dft_inreg(float2 *v) {
+  static_for<1, ilog2(R) + 1>([&](auto s) {
+    constexpr int LEN = 1 << decltype(s)::value;
+    static_for<0, R / 2>([&](auto i) {
+      constexpr int I = decltype(i)::value;
+      constexpr int blk = (I / (LEN / 2)) * LEN;
+      constexpr int j = I % (LEN / 2);
+      bfly<j * (32 / LEN), INV>(v[blk + j], v[blk + j + LEN / 2]);
+    });
+  });
+}
+
+// Powers of a per-thread twiddle base w: w^k for k in [1,R).  Two-level scheme
+// (w^(4a+b) = w^(4a) * w^b) so that only R/4+2 powers are live at once and every power is at
+// most log2(R) multiplications away from the tabulated base.
+template <int R>
+struct Powers {
+  float2 lo[4];
+  float2 hi[R / 4 > 0 ? R / 4 : 1];
+  FC_HD void init(float2 w) {
+    lo[1] = w;
+    if constexpr (R > 2) {
+      lo[2] = cmul(w, w);
+      lo[3] = cmul(lo[2], w);
+    }
+    if constexpr (R > 4) {
+      hi[1] = cmul(lo[2], lo[2]);
+      static_for<2, R / 4>([&](auto a) {
+        constexpr int A = decltype(a)::value;
+        constexpr int H = hibit(A);
+        if constexpr (H == A) hi[A] = cmul(hi[A / 2], hi[A / 2]);
+        else hi[A] = cmul(hi[H], hi[A - H]);
+      });
+    }
+  }
+  template <int K>
+  FC_HD float2 get() const {
+    constexpr int a = K >> 2, b = K & 3;
+    if constexpr (a == 0) return lo[b];
+    else if constexpr (b == 0) return hi[a];
+    else return cmul(hi[a], lo[b]);
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// Plan: N complex points held by T = N/E threads, E points per thread in registers.
+template <int N_, int E_, int R1_, int R2_, int R3_>
+struct Plan {
+  static constexpr int N = N_, E = E_, R1 = R1_, R2 = R2_, R3 = R3_;
+  static constexpr int T = N / E;
+  static constexpr int NPASS = R2 > 1 ? 3 : 2;
+  static constexpr int NB2 = N / R1;          // block length seen by the 2nd pass
+  static constexpr int NBF3 = N / R3;         // butterflies in the last (contiguous) pass
+  static constexpr int SMEM_FLOAT2 = padded_len(N);
+  static_assert(R1 * R2 * R3 == N, "radices must multiply to N");
+  static_assert(E % R1 == 0 && E % R2 == 0 && E % R3 == 0, "E must be a multiple of each radix");
+  static_assert(NPASS == 3 || R3 == NB2, "two-pass plan: R3 = N/R1");
+};
+
+// Where butterfly number j of thread t lives for a pass with block length NB and radix R.
+template <class P, int NB, int R>
+struct PassGeom {
+  static constexpr int S = NB / R;            // stride between a butterfly's elements
+  FC_HD static void locate(int t, int j, int &base, int &npp, int &bf) {
+    bf = t + j * P::T;
+    int blk = bf / S;
+    npp = bf % S;
+    base = blk * NB + npp;
+  }
+};
+
+// Description of one unit of work: a pair of overlap-save segments of one signal.
+struct SegPair {
+  const float *x;      // signal base
+  i64 x_len;           // valid samples; X(i) = 0 outside [0, x_len)
+  i64 inA;             // X index of segment A's sample 0 (may be negative)
+  i64 inB;             // same for segment B
+  bool haveB;
+  float *out;          // result base of this signal
+  i64 outA, outB;      // out index receiving c[c_off] of each segment
+  int cntA, cntB;      // number of valid outputs of each segment (<= step), 0 = none
+  int c_off;           // first useful circular-convolution sample (h_len - 1 in OS)
+  bool accumulate;     // add to out instead of overwriting (partitioned impulse response)
+};
+
+FC_HD float load_x(const float *x, i64 x_len, i64 i) {
+  return (i >= 0 && i < x_len) ? x[i] : 0.0f;
+}
+
+// forward first pass: global -> registers -> R1-point DFT -> twiddle -> shared memory
+template <class P>
+FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  const bool fastA = w.inA >= 0 && w.inA + P::N <= w.x_len;
+  const bool fastB = w.haveB && w.inB >= 0 && w.inB + P::N <= w.x_len;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      int p = base + r * G::S;
+      float a, b;
+      if (fastA) a = w.x[w.inA + p]; else a = load_x(w.x, w.x_len, w.inA + p);
+      if (fastB) b = w.x[w.inB + p];
+      else b = w.haveB ? load_x(w.x, w.x_len, w.inB + p) : 0.0f;
+      v[bitrev(r, ilog2(R))] = make_float2(a, b);
+    });
+    dft_inreg<R, false>(v);
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tw[npp * (P::N / NB)]);
+      static_for<1, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        v[k] = cmul(v[k], pw.template get<k>());
+      });
+    }
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      sm[pad_pos(base + k * G::S)] = v[k];
+    });
+  });
+}
+
+// forward middle pass (3-pass plans only): shared -> DFT_R2 -> twiddle -> shared (in place)
+template <class P>
+FC_HD void fwd_mid(int t, const float2 *tw, float2 *sm) {
+  constexpr int R = P::R2, NB = P::NB2;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = sm[pad_pos(base + r * G::S)];
+    });
+    dft_inreg<R, false>(v);
+    Powers<R> pw;
+    pw.init(tw[npp * (P::N / NB)]);
+    static_for<1, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      v[k] = cmul(v[k], pw.template get<k>());
+    });
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      sm[pad_pos(base + k * G::S)] = v[k];
+    });
+  });
+}
+
+// centre: last forward pass, pointwise product with the filter spectrum, first inverse pass.
+// Hperm layout: bin held in register k of butterfly bf is Hperm[k * NBF3 + bf].
+template <class P>
+FC_HD void centre(int t, const float2 *Hperm, float2 *sm) {
+  constexpr int R = P::R3;
+  using G = PassGeom<P, R, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R], u[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = sm[pad_pos(base + r)];
+    });
+    dft_inreg<R, false>(v);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      u[bitrev(k, ilog2(R))] = cmul(v[k], Hperm[k * P::NBF3 + bf]);
+    });
+    dft_inreg<R, true>(u);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      sm[pad_pos(base + r)] = u[r];
+    });
+  });
+}
+
+// spectrum variant of the centre: last forward pass, then write bins * scale to Hperm.
+template <class P>
+FC_HD void centre_store_spectrum(int t, float2 *Hperm, float scale, const float2 *sm) {
+  constexpr int R = P::R3;
+  using G = PassGeom<P, R, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = sm[pad_pos(base + r)];
+    });
+    dft_inreg<R, false>(v);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      Hperm[k * P::NBF3 + bf] = make_float2(v[k].x * scale, v[k].y * scale);
+    });
+  });
+}
+
+// inverse middle pass (3-pass plans only): shared -> conj twiddle -> IDFT_R2 -> shared
+template <class P>
+FC_HD void inv_mid(int t, const float2 *tw, float2 *sm) {
+  constexpr int R = P::R2, NB = P::NB2;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R];
+    Powers<R> pw;
+    pw.init(tw[npp * (P::N / NB)]);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      float2 e = sm[pad_pos(base + k * G::S)];
+      if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
+      v[bitrev(k, ilog2(R))] = e;
+    });
+    dft_inreg<R, true>(v);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      sm[pad_pos(base + r * G::S)] = v[r];
+    });
+  });
+}
+
+// inverse last pass: shared -> conj twiddle -> IDFT_R1 -> global (real part -> segment A,
+// imaginary part -> segment B), keeping only circular samples >= c_off.
+template <class P>
+FC_HD void inv_last(int t, const SegPair &w, const float2 *tw, const float2 *sm) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R];
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tw[npp * (P::N / NB)]);
+      static_for<0, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        float2 e = sm[pad_pos(base + k * G::S)];
+        if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
+        v[bitrev(k, ilog2(R))] = e;
+      });
+    } else {
+      static_for<0, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        v[bitrev(k, ilog2(R))] = sm[pad_pos(base + k * G::S)];
+      });
+    }
+    dft_inreg<R, true>(v);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      int p = base + r * G::S;          // natural-order circular index
+      int tt = p - w.c_off;
+      if (tt >= 0) {
+        if (tt < w.cntA) {
+          float *o = w.out + (w.outA + tt);
+          *o = w.accumulate ? *o + v[r].x : v[r].x;
+        }
+        if (tt < w.cntB) {
+          float *o = w.out + (w.outB + tt);
+          *o = w.accumulate ? *o + v[r].y : v[r].y;
+        }
+      }
+    });
+  });
+}
+
+// Filter-spectrum first pass: zero-padded real impulse response gf[m] = h[start + dir*m]
+// (m < taps) -> registers -> DFT -> twiddle -> shared.
+template <class P>
+FC_HD void spec_first(int t, const float *h, i64 start, int dir, int taps,
+                      const float2 *tw, float2 *sm) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    float2 v[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      int p = base + r * G::S;
+      float a = p < taps ? h[start + (i64)dir * p] : 0.0f;
+      v[bitrev(r, ilog2(R))] = make_float2(a, 0.0f);
+    });
+    dft_inreg<R, false>(v);
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tw[npp * (P::N / NB)]);
+      static_for<1, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        v[k] = cmul(v[k], pw.template get<k>());
+      });
+    }
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      sm[pad_pos(base + k * G::S)] = v[k];
+    });
+  });
+}
+
+}  // namespace fc

@@ -1,0 +1,264 @@
+// os_fft.cu -- fused overlap-save / FFT convolution kernels.
+//
+// Replaces convolve_overlap_save (/root/reference/src/convolve.c:156-229) and convolve_fft
+// (/root/reference/src/convolve.c:289-326).  The reference walks the segments serially and
+// per segment runs: gather -> FFTF forward -> complex multiply with the filter spectrum ->
+// FFTF inverse -> scale -> copy.  Here one CTA does all of that for a PAIR of segments
+// (packed as real + i*imag of one complex transform, see fft_core.cuh) without the spectrum
+// ever leaving the SM: global -> registers -> (shared-memory passes) -> registers -> global.
+//
+// Kernels:
+//   os_spectrum_kernel<P>   H = FFT_N(zero-pad(h or reversed h)) / N, written in the register
+//                           order of the fused kernel's centre pass (src/convolve.c:167-176:
+//                           the reference also rebuilds H on every call because h is a call
+//                           argument).  One CTA per impulse-response partition.
+//   os_fused_kernel<P, G>   one CTA = G independent segment pairs of P::N complex points.
+//
+// Segment length is NOT the reference's L = 4*2^floor(log2 h) (src/convolve.c:116-121); it
+// is chosen per impulse-response length from the plans below (b200_os_pick_n).  Impulse
+// responses longer than one transform can hold are split into partitions of part_taps taps;
+// each partition is one launch accumulating into the result (uniformly partitioned
+// overlap-save), which also serves the whole-signal "FFT" algorithm for long inputs.
+#include "b200_device.cuh"
+#include "fft_core.cuh"
+#include <math.h>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+using namespace fc;
+
+struct OsParams {
+  const float *x;
+  i64 x_len, x_stride;
+  float *out;
+  i64 out_len, out_stride;
+  const float2 *spectrum;   // this partition's filter spectrum
+  const float2 *tw;
+  i64 in_shift;             // X index of segment 0's first sample
+  int c_off;                // first useful circular sample
+  int step;                 // outputs per segment
+  i64 nseg;                 // segments per signal
+  i64 npairs;               // segment pairs per signal
+  i64 total;                // npairs * batch
+  int accumulate;
+};
+
+struct SpecParams {
+  const float *h;
+  i64 h_len;
+  int reverse;
+  int part_taps;
+  float2 *spectrum;         // [parts][N]
+  const float2 *tw;
+  float scale;
+};
+
+template <class P>
+__global__ void __launch_bounds__(P::T) os_spectrum_kernel(SpecParams p) {
+  extern __shared__ float4 smem4[];
+  float2 *sm = reinterpret_cast<float2 *>(smem4);
+  const int t = threadIdx.x;
+  const int part = blockIdx.x;
+  // correlation-form taps of this partition: g[j], j in [j0, j0+taps); its convolution-form
+  // impulse response is gf[m] = g[j0+taps-1-m]  (g[j] = reverse ? h[j] : h[h_len-1-j]).
+  const i64 j0 = (i64)part * p.part_taps;
+  const i64 left = p.h_len - j0;
+  const int taps = (int)(left < p.part_taps ? left : p.part_taps);
+  i64 start;
+  int dir;
+  if (p.reverse) { start = j0 + taps - 1; dir = -1; }
+  else { start = p.h_len - j0 - taps; dir = 1; }
+  spec_first<P>(t, p.h, start, dir, taps, p.tw, sm);
+  __syncthreads();
+  if constexpr (P::NPASS == 3) {
+    fwd_mid<P>(t, p.tw, sm);
+    __syncthreads();
+  }
+  centre_store_spectrum<P>(t, p.spectrum + (size_t)part * P::N, p.scale, sm);
+}
+
+template <class P, int G>
+__global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
+  extern __shared__ float4 smem4[];
+  const int grp = threadIdx.x / P::T;
+  const int t = threadIdx.x % P::T;
+  float2 *sm = reinterpret_cast<float2 *>(smem4) + grp * P::SMEM_FLOAT2;
+
+  const i64 item = (i64)blockIdx.x * G + grp;
+  const bool live = item < p.total;     // whole group idles (but still hits the barriers)
+  SegPair w;
+  if (live) {
+    const i64 b = item / p.npairs;
+    const i64 sa = (item % p.npairs) * 2;
+    w.x = p.x + b * p.x_stride;
+    w.x_len = p.x_len;
+    w.inA = sa * p.step + p.in_shift;
+    w.inB = w.inA + p.step;
+    w.haveB = sa + 1 < p.nseg;
+    w.out = p.out + b * p.out_stride;
+    w.outA = sa * p.step;
+    w.outB = w.outA + p.step;
+    const i64 remA = p.out_len - w.outA, remB = p.out_len - w.outB;
+    w.cntA = (int)(remA < p.step ? remA : p.step);
+    w.cntB = w.haveB ? (int)(remB < p.step ? remB : p.step) : 0;
+    w.c_off = p.c_off;
+    w.accumulate = p.accumulate != 0;
+    fwd_first<P>(t, w, p.tw, sm);
+  }
+  __syncthreads();
+  if constexpr (P::NPASS == 3) {
+    if (live) fwd_mid<P>(t, p.tw, sm);
+    __syncthreads();
+  }
+  if (live) centre<P>(t, p.spectrum, sm);
+  __syncthreads();
+  if constexpr (P::NPASS == 3) {
+    if (live) inv_mid<P>(t, p.tw, sm);
+    __syncthreads();
+  }
+  if (live) inv_last<P>(t, w, p.tw, sm);
+}
+
+// ---- plan table ---------------------------------------------------------------------------
+// N         radices      E   threads/transform   transforms per CTA
+using P256 = Plan<256, 16, 16, 1, 16>;      // 16                8
+using P512 = Plan<512, 16, 2, 16, 16>;      // 32                4
+using P1024 = Plan<1024, 16, 4, 16, 16>;    // 64                2
+using P2048 = Plan<2048, 16, 8, 16, 16>;    // 128               1
+using P4096 = Plan<4096, 16, 16, 16, 16>;   // 256               1
+using P8192 = Plan<8192, 32, 32, 16, 16>;   // 256               1
+using P16384 = Plan<16384, 32, 32, 32, 16>; // 512               1
+
+template <class P, int G>
+void launch_fused(const OsParams &p, cudaStream_t stream) {
+  static bool configured[16] = {false};
+  size_t smem = sizeof(float2) * P::SMEM_FLOAT2 * G;
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 16 && !configured[dev]) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(os_fused_kernel<P, G>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev] = true;
+  }
+  i64 blocks = (p.total + G - 1) / G;
+  B200_REQUIRE(blocks < 2147483647LL, "overlap-save grid too large");
+  b200_prof_begin(B200_PROF_FUSED, stream);
+  os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(p);
+  b200_prof_end(B200_PROF_FUSED, stream);
+  B200_CUDA_CHECK(cudaGetLastError());
+  b200_count_launch(1);
+}
+
+template <class P>
+void launch_spectrum(const SpecParams &p, int parts, cudaStream_t stream) {
+  static bool configured[16] = {false};
+  size_t smem = sizeof(float2) * P::SMEM_FLOAT2;
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 16 && !configured[dev]) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(os_spectrum_kernel<P>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev] = true;
+  }
+  b200_prof_begin(B200_PROF_SPECTRUM, stream);
+  os_spectrum_kernel<P><<<parts, P::T, smem, stream>>>(p);
+  b200_prof_end(B200_PROF_SPECTRUM, stream);
+  B200_CUDA_CHECK(cudaGetLastError());
+  b200_count_launch(1);
+}
+
+struct TwiddleCache {
+  std::mutex mu;
+  const float2 *tab[16][16] = {};   // [device][log2 n]
+};
+TwiddleCache g_tw;
+
+}  // namespace
+
+// Twiddle table W_n^j = exp(-2*pi*i*j/n), j < n/2, computed in double on the host once per
+// device and transform length, kept for the life of the process (<= 64 KB each).
+const float2 *b200_twiddles(int n_fft) {
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev < 16, "device index out of range");
+  int lg = 0;
+  while ((1 << lg) < n_fft) lg++;
+  std::lock_guard<std::mutex> lock(g_tw.mu);
+  if (g_tw.tab[dev][lg]) return g_tw.tab[dev][lg];
+  int cnt = n_fft / 2 > 0 ? n_fft / 2 : 1;
+  std::vector<float2> host(cnt);
+  const double pi2 = 6.283185307179586476925286766559;
+  for (int j = 0; j < cnt; j++) {
+    double a = -pi2 * j / n_fft;
+    host[j] = make_float2((float)cos(a), (float)sin(a));
+  }
+  float2 *dptr = nullptr;
+  B200_CUDA_CHECK(cudaMalloc(&dptr, sizeof(float2) * cnt));
+  B200_CUDA_CHECK(cudaMemcpy(dptr, host.data(), sizeof(float2) * cnt, cudaMemcpyHostToDevice));
+  g_tw.tab[dev][lg] = dptr;
+  return dptr;
+}
+
+void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part_taps,
+                         const DevJob &job, bool single_segment, cudaStream_t stream) {
+  if (job.batch <= 0 || job.out_len <= 0) return;
+  const int parts = (int)((job.h_len + part_taps - 1) / part_taps);
+
+  SpecParams sp;
+  sp.h = job.h; sp.h_len = job.h_len; sp.reverse = job.reverse;
+  sp.part_taps = part_taps; sp.spectrum = spectrum; sp.tw = tw;
+  sp.scale = 1.0f / (float)n_fft;
+
+  OsParams op;
+  op.x = job.x; op.x_len = job.x_len; op.x_stride = job.x_stride;
+  op.out = job.out; op.out_len = job.out_len; op.out_stride = job.out_stride;
+  op.tw = tw;
+
+#define B200_DISPATCH(PLAN, GROUPS)                                                    \
+  case PLAN::N: {                                                                      \
+    launch_spectrum<PLAN>(sp, parts, stream);                                          \
+    for (int q = 0; q < parts; q++) {                                                  \
+      const i64 j0 = (i64)q * part_taps;                                               \
+      const i64 left = job.h_len - j0;                                                 \
+      const int taps = (int)(left < part_taps ? left : part_taps);                     \
+      op.spectrum = spectrum + (size_t)q * PLAN::N;                                    \
+      op.accumulate = q > 0;                                                           \
+      if (single_segment) {                                                            \
+        /* whole-signal transform: leading zeros implicit, no wrapped outputs needed */ \
+        op.in_shift = 0; op.c_off = 0; op.step = PLAN::N;                              \
+        B200_REQUIRE(parts == 1 && job.pad == job.h_len - 1 &&                         \
+                     job.out_len <= PLAN::N && job.x_len + job.h_len - 1 <= PLAN::N,   \
+                     "single-segment FFT does not fit the transform");                 \
+      } else {                                                                         \
+        op.in_shift = j0 - job.pad; op.c_off = taps - 1; op.step = PLAN::N - taps + 1; \
+      }                                                                                \
+      op.nseg = (job.out_len + op.step - 1) / op.step;                                 \
+      op.npairs = (op.nseg + 1) / 2;                                                   \
+      op.total = op.npairs * job.batch;                                                \
+      launch_fused<PLAN, GROUPS>(op, stream);                                          \
+    }                                                                                  \
+  } break;
+
+  switch (n_fft) {
+    B200_DISPATCH(P256, 8)
+    B200_DISPATCH(P512, 4)
+    B200_DISPATCH(P1024, 2)
+    B200_DISPATCH(P2048, 1)
+    B200_DISPATCH(P4096, 1)
+    B200_DISPATCH(P8192, 1)
+    B200_DISPATCH(P16384, 1)
+    default:
+      B200_REQUIRE(false, "unsupported transform length");
+  }
+#undef B200_DISPATCH
+}
+
+void b200_os_launch(const OsDevPlan &plan, const DevJob &job, bool single_segment,
+                    cudaStream_t stream) {
+  const int parts = (int)((job.h_len + plan.part_taps - 1) / plan.part_taps);
+  B200_REQUIRE(parts <= plan.max_parts, "impulse response longer than the plan was sized for");
+  b200_os_launch_with(plan.twiddles, plan.spectrum, plan.n_fft, plan.part_taps, job,
+                      single_segment, stream);
+}
