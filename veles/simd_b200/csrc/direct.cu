@@ -7,13 +7,18 @@
 // convolution and g = h for correlation, so one kernel serves both; the reference's
 // per-output beg/end clamps (convolve.c:51-55, correlate.c:80-84) become a zero-filled halo.
 //
-// Layout: a CTA owns TILE = R*TPB consecutive outputs of one signal.  It stages the x window
-// [n0 - pad, n0 - pad + TILE + hc - 1) and the tap block g[c0, c0+hc) in shared memory with
-// coalesced loads, then every thread accumulates R = 16 consecutive outputs in registers,
-// sliding a 32-sample register window over the tile so that each 16-byte shared-memory read
-// feeds 64 FMAs.  The x tile is stored with 4 pad floats per 16 so that the 64-byte-strided
-// float4 reads of a quarter warp hit 8 distinct bank groups.  Results go back through shared
-// memory so the global stores are fully coalesced for any row alignment.
+// Layout: a CTA owns a strip of consecutive TILE = R*TPB output tiles of one signal.  For
+// each tile the x window [n0 - pad, n0 - pad + TILE + taps - 1) is staged in shared memory
+// with cp.async (LDGSTS, zero-filled outside the signal) into one of two buffers, so the
+// next tile's loads are in flight while the current tile is computed.  Every thread
+// accumulates R = 16 consecutive outputs in registers, sliding a 32-sample register window
+// over the tile so that each 16-byte shared-memory read feeds 64 FMAs.  The x tile is stored
+// with 4 pad floats per 16 so that the 64-byte-strided float4 reads of a quarter warp hit 8
+// distinct bank groups.  Results go back through shared memory so the global stores are
+// fully coalesced for any row alignment.
+//
+// Impulse responses longer than kMaxHC taps (not what the selector sends here, but legal
+// through convolve_simd) take the unpipelined multi-pass kernel.
 //
 // Roofline: 2*h_len FLOP and 8 B of HBM traffic per output -> FP32-bound above h_len ~ 45.
 #include "b200_device.cuh"
@@ -24,6 +29,7 @@ constexpr int kR = 16;          // outputs per thread
 constexpr int kTPB = 128;       // threads per CTA
 constexpr int kTile = kR * kTPB;
 constexpr int kMaxHC = 1024;    // taps staged per pass over the tile
+constexpr int kMaxStrip = 16;   // tiles per CTA in the pipelined kernel
 
 __device__ __forceinline__ int padx(int q) { return q + ((q >> 4) << 2); }
 
@@ -36,14 +42,152 @@ struct DirectParams {
   i64 out_len, out_stride;
   i64 pad;
   i64 tiles_per_signal;
+  i64 strips_per_signal;
+  int strip;            // tiles per CTA
   int reverse;
   int hc_max;           // taps per staging pass (multiple of 16)
+  int xbuf_floats;      // size of one padded x buffer
 };
 
+__device__ __forceinline__ void cp_async4(float *smem_dst, const float *gsrc, bool valid) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  int sz = valid ? 4 : 0;      // src-size 0 -> the 4 destination bytes are zero-filled
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+// acc[r] += sum_{j < hc} gs[j] * xs[t0 + r + j], r < 16; xrow = xs + padx(t0)
+__device__ __forceinline__ void accumulate_taps(float (&acc)[kR], const float *gs,
+                                                const float *xrow, int hc) {
+  const int hc16 = hc & ~15;
+  float w[32];
+  if (hc16 > 0) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      float4 v = *reinterpret_cast<const float4 *>(xrow + 4 * i);
+      w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+    }
+  }
+  for (int j0 = 0; j0 < hc16; j0 += 16) {
+    const float *xn = xrow + ((j0 + 16) >> 4) * 20;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      float4 v = *reinterpret_cast<const float4 *>(xn + 4 * i);
+      w[16 + 4 * i] = v.x; w[17 + 4 * i] = v.y; w[18 + 4 * i] = v.z; w[19 + 4 * i] = v.w;
+    }
+#pragma unroll
+    for (int q4 = 0; q4 < 4; q4++) {
+      float4 g = *reinterpret_cast<const float4 *>(gs + j0 + 4 * q4);
+      const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int jj = 0; jj < 4; jj++) {
+#pragma unroll
+        for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], w[r + 4 * q4 + jj], acc[r]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i++) w[i] = w[i + 16];
+  }
+  // remaining (< 16) taps, four at a time with exact tap predicates
+  for (int j0 = hc16; j0 < hc; j0 += 4) {
+    const int blk = j0 >> 4, off = j0 & 15;    // off in {0,4,8,12}
+    const float *xa = xrow + blk * 20 + off;
+    float wr[20];
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+      // the 20-sample window may straddle one row boundary (rows are 16 data + 4 pad)
+      const float *src = xa + 4 * i + (off + 4 * i >= 16 ? 4 : 0);
+      float4 v = *reinterpret_cast<const float4 *>(src);
+      wr[4 * i] = v.x; wr[4 * i + 1] = v.y; wr[4 * i + 2] = v.z; wr[4 * i + 3] = v.w;
+    }
+    float4 g = *reinterpret_cast<const float4 *>(gs + j0);
+    const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+      if (j0 + jj < hc) {
+#pragma unroll
+        for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], wr[r + jj], acc[r]);
+      }
+    }
+  }
+}
+
+// ---- pipelined kernel: all taps fit one staging pass (h_len <= kMaxHC) -------------------
 __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
   extern __shared__ float4 smem4[];
   float *gs = reinterpret_cast<float *>(smem4);          // hc_max + 16 taps
-  float *xs = gs + p.hc_max + 16;                        // padded x window
+  float *xbuf0 = gs + p.hc_max + 16;                     // two padded x windows
+
+  const int tid = threadIdx.x;
+  const i64 b = blockIdx.x / p.strips_per_signal;
+  const i64 tile0 = (blockIdx.x % p.strips_per_signal) * p.strip;
+  const i64 tile_end = tile0 + p.strip < p.tiles_per_signal ? tile0 + p.strip : p.tiles_per_signal;
+  const float *xb = p.x + b * p.x_stride;
+  float *ob = p.out + b * p.out_stride;
+  const int hc = (int)p.h_len;
+  const int wlen = kTile + hc - 1;
+  const int t0 = tid * kR;
+
+  auto stage = [&](i64 tile, float *xs) {
+    const i64 xi0 = tile * kTile - p.pad;
+    const float *src = xb + xi0;
+    if (xi0 >= 0 && xi0 + wlen <= p.x_len) {
+#pragma unroll 4
+      for (int q = tid; q < wlen; q += kTPB) cp_async4(xs + padx(q), src + q, true);
+    } else {
+#pragma unroll 2
+      for (int q = tid; q < wlen; q += kTPB) {
+        const i64 i = xi0 + q;
+        const bool ok = i >= 0 && i < p.x_len;
+        cp_async4(xs + padx(q), ok ? src + q : xb, ok);
+      }
+    }
+    cp_async_commit();
+  };
+
+  stage(tile0, xbuf0);
+  for (int j = tid; j < hc; j += kTPB) gs[j] = p.reverse ? p.h[j] : p.h[p.h_len - 1 - j];
+
+  int buf = 0;
+  for (i64 tile = tile0; tile < tile_end; tile++, buf ^= 1) {
+    float *xs = xbuf0 + buf * p.xbuf_floats;
+    cp_async_wait_all();
+    __syncthreads();                       // tile's window (and the taps) visible to all;
+                                           // the other buffer is no longer being read
+    if (tile + 1 < tile_end) stage(tile + 1, xbuf0 + (buf ^ 1) * p.xbuf_floats);
+
+    const i64 n0 = tile * kTile;
+    const i64 remaining = p.out_len - n0;
+    const int cnt = remaining < kTile ? (int)remaining : kTile;
+    const bool active = ((tid & ~31) * kR) < cnt;    // warp-uniform
+    float acc[kR];
+#pragma unroll
+    for (int r = 0; r < kR; r++) acc[r] = 0.f;
+    if (active) accumulate_taps(acc, gs, xs + padx(t0), hc);
+
+    // results -> shared (same padded rows) -> coalesced global stores
+    __syncthreads();
+    if (active) {
+      float *orow = xs + padx(t0);
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        *reinterpret_cast<float4 *>(orow + 4 * i) =
+            make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
+      }
+    }
+    __syncthreads();
+    float *o = ob + n0;
+#pragma unroll 4
+    for (int i = tid; i < cnt; i += kTPB) o[i] = xs[padx(i)];
+  }
+}
+
+// ---- unpipelined kernel for very long impulse responses (several staging passes) ---------
+__global__ void __launch_bounds__(kTPB, 4) direct_long_kernel(DirectParams p) {
+  extern __shared__ float4 smem4[];
+  float *gs = reinterpret_cast<float *>(smem4);
+  float *xs = gs + p.hc_max + 16;
 
   const int tid = threadIdx.x;
   const i64 tile = blockIdx.x;
@@ -53,7 +197,6 @@ __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
   const i64 remaining = p.out_len - n0;
   const int cnt = remaining < kTile ? (int)remaining : kTile;
   const int t0 = tid * kR;
-  // warp-uniform: does any thread of this warp own a live output?
   const bool active = ((tid & ~31) * kR) < cnt;
 
   float acc[kR];
@@ -63,84 +206,21 @@ __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
   for (i64 c0 = 0; c0 < p.h_len; c0 += p.hc_max) {
     const int hc = (int)((p.h_len - c0) < p.hc_max ? (p.h_len - c0) : p.hc_max);
     if (c0 > 0) __syncthreads();
-    // taps of this pass, correlation order
     for (int j = tid; j < hc; j += kTPB) {
       i64 gj = c0 + j;
       gs[j] = p.reverse ? p.h[gj] : p.h[p.h_len - 1 - gj];
     }
-    // x window of this pass (zero outside the signal)
     const i64 xi0 = n0 + c0 - p.pad;
     const int wlen = kTile + hc - 1;
-    if (xi0 >= 0 && xi0 + wlen <= p.x_len) {
-#pragma unroll 8
-      for (int q = tid; q < wlen; q += kTPB) xs[padx(q)] = xb[xi0 + q];
-    } else {
 #pragma unroll 4
-      for (int q = tid; q < wlen; q += kTPB) {
-        i64 i = xi0 + q;
-        xs[padx(q)] = (i >= 0 && i < p.x_len) ? xb[i] : 0.f;
-      }
+    for (int q = tid; q < wlen; q += kTPB) {
+      i64 i = xi0 + q;
+      xs[padx(q)] = (i >= 0 && i < p.x_len) ? xb[i] : 0.f;
     }
     __syncthreads();
-
-    if (active) {
-      const int hc16 = hc & ~15;
-      float w[32];
-      const float *xrow = xs + padx(t0);     // t0 is a multiple of 16: 20-float rows from here
-      if (hc16 > 0) {
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-          float4 v = *reinterpret_cast<const float4 *>(xrow + 4 * i);
-          w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-        }
-      }
-      for (int j0 = 0; j0 < hc16; j0 += 16) {
-        const float *xn = xrow + ((j0 + 16) >> 4) * 20;
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-          float4 v = *reinterpret_cast<const float4 *>(xn + 4 * i);
-          w[16 + 4 * i] = v.x; w[17 + 4 * i] = v.y; w[18 + 4 * i] = v.z; w[19 + 4 * i] = v.w;
-        }
-#pragma unroll
-        for (int q4 = 0; q4 < 4; q4++) {
-          float4 g = *reinterpret_cast<const float4 *>(gs + j0 + 4 * q4);
-          const float gg[4] = {g.x, g.y, g.z, g.w};
-#pragma unroll
-          for (int jj = 0; jj < 4; jj++) {
-#pragma unroll
-            for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], w[r + 4 * q4 + jj], acc[r]);
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 16; i++) w[i] = w[i + 16];
-      }
-      // remaining (< 16) taps, four at a time with exact tap predicates
-      for (int j0 = hc16; j0 < hc; j0 += 4) {
-        const int blk = j0 >> 4, off = j0 & 15;    // off in {0,4,8,12}
-        const float *xa = xrow + blk * 20 + off;
-        float wr[20];
-#pragma unroll
-        for (int i = 0; i < 5; i++) {
-          // the 20-sample window may straddle one row boundary
-          int e = off + 4 * i;
-          const float *src = xa + 4 * i + (e >= 16 ? 4 : 0) + (e >= 32 ? 4 : 0);
-          float4 v = *reinterpret_cast<const float4 *>(src);
-          wr[4 * i] = v.x; wr[4 * i + 1] = v.y; wr[4 * i + 2] = v.z; wr[4 * i + 3] = v.w;
-        }
-        float4 g = *reinterpret_cast<const float4 *>(gs + j0);
-        const float gg[4] = {g.x, g.y, g.z, g.w};
-#pragma unroll
-        for (int jj = 0; jj < 4; jj++) {
-          if (j0 + jj < hc) {
-#pragma unroll
-            for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], wr[r + jj], acc[r]);
-          }
-        }
-      }
-    }
+    if (active) accumulate_taps(acc, gs, xs + padx(t0), hc);
   }
 
-  // results -> shared (same padded rows) -> coalesced global stores
   __syncthreads();
   if (active) {
     float *orow = xs + padx(t0);
@@ -168,12 +248,29 @@ void b200_direct_launch(const DevJob &job, cudaStream_t stream) {
   p.tiles_per_signal = (job.out_len + kTile - 1) / kTile;
   i64 hc = job.h_len < kMaxHC ? job.h_len : kMaxHC;
   p.hc_max = (int)((hc + 15) & ~15LL);
-  i64 tiles = p.tiles_per_signal * job.batch;
-  B200_REQUIRE(tiles < 2147483647LL, "direct kernel grid too large");
-  // taps (+16 slack for the float4 tail read) + padded x window (+ two slack rows)
-  size_t smem = sizeof(float) * (size_t)(p.hc_max + 16 + ((kTile + p.hc_max + 32) / 16 + 1) * 20);
+  // padded x window (+ two slack rows for the float4 tail reads)
+  p.xbuf_floats = ((kTile + p.hc_max + 32) / 16 + 1) * 20;
+  const i64 tiles = p.tiles_per_signal * job.batch;
   b200_prof_begin(B200_PROF_DIRECT, stream);
-  direct_kernel<<<(unsigned)tiles, kTPB, smem, stream>>>(p);
+  if (job.h_len <= kMaxHC) {
+    // strips long enough to amortise the pipeline prologue, short enough to fill the GPU
+    i64 strip = tiles / (148 * 10);
+    if (strip < 1) strip = 1;
+    if (strip > kMaxStrip) strip = kMaxStrip;
+    if (strip > p.tiles_per_signal) strip = p.tiles_per_signal;
+    p.strip = (int)strip;
+    p.strips_per_signal = (p.tiles_per_signal + strip - 1) / strip;
+    const i64 blocks = p.strips_per_signal * job.batch;
+    B200_REQUIRE(blocks < 2147483647LL, "direct kernel grid too large");
+    size_t smem = sizeof(float) * (size_t)(p.hc_max + 16 + 2 * p.xbuf_floats);
+    direct_kernel<<<(unsigned)blocks, kTPB, smem, stream>>>(p);
+  } else {
+    p.strip = 1;
+    p.strips_per_signal = p.tiles_per_signal;
+    B200_REQUIRE(tiles < 2147483647LL, "direct kernel grid too large");
+    size_t smem = sizeof(float) * (size_t)(p.hc_max + 16 + p.xbuf_floats);
+    direct_long_kernel<<<(unsigned)tiles, kTPB, smem, stream>>>(p);
+  }
   b200_prof_end(B200_PROF_DIRECT, stream);
   B200_CUDA_CHECK(cudaGetLastError());
   b200_count_launch(1);

@@ -31,6 +31,7 @@
 #pragma once
 
 #include <type_traits>
+#include <math.h>
 
 #if defined(__CUDACC__)
 #define FC_HD __host__ __device__ __forceinline__
@@ -77,10 +78,10 @@ FC_HD constexpr int ilog2(int v) { int l = 0; while ((1 << l) < v) l++; return l
 FC_HD constexpr int hibit(int v) { int h = 1; while (h * 2 <= v) h *= 2; return h; }
 
 FC_HD float2 cmul(float2 a, float2 b) {
-  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+  return make_float2(fmaf(a.x, b.x, -(a.y * b.y)), fmaf(a.x, b.y, a.y * b.x));
 }
 FC_HD float2 cmul_conj(float2 a, float2 b) {   // a * conj(b)
-  return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
+  return make_float2(fmaf(a.x, b.x, a.y * b.y), fmaf(a.y, b.x, -(a.x * b.y)));
 }
 
 // One radix-2 DIT butterfly with compile-time twiddle w = W_32^K32 (forward:
@@ -100,11 +101,10 @@ FC_HD void bfly(float2 &a, float2 &b) {
   } else {
     constexpr float wr = cos32(K32);
     constexpr float wi = INV ? sin32(K32) : -sin32(K32);
-    float nr = a.x + b.x * wr;
-    nr = nr - b.y * wi;
-    float ni = a.y + b.x * wi;
-    ni = ni + b.y * wr;
-    b = make_float2(2.0f * a.x - nr, 2.0f * a.y - ni);
+    // explicit fmaf: the compiler otherwise rewrites 2*a as a+a and splits the last FMA
+    const float nr = fmaf(-b.y, wi, fmaf(b.x, wr, a.x));
+    const float ni = fmaf(b.y, wr, fmaf(b.x, wi, a.y));
+    b = make_float2(fmaf(2.0f, a.x, -nr), fmaf(2.0f, a.y, -ni));
     a = make_float2(nr, ni);
   }
 }
@@ -175,12 +175,17 @@ struct Plan {
 template <class P, int NB, int R>
 struct PassGeom {
   static constexpr int S = NB / R;            // stride between a butterfly's elements
+  static_assert(S == 1 || S % 16 == 0, "strides are 1 or multiples of the pad period");
   FC_HD static void locate(int t, int j, int &base, int &npp, int &bf) {
     bf = t + j * P::T;
     int blk = bf / S;
     npp = bf % S;
     base = blk * NB + npp;
   }
+  // Padded shared-memory offset of element r relative to pad_pos(base): a compile-time
+  // constant, because r*S is a multiple of 16 (S % 16 == 0) or stays inside base's 16-slot
+  // row (S == 1, base % 16 == 0, r < 16).
+  FC_HD static constexpr int off(int r) { return S == 1 ? r : r * S + (r * S) / 16; }
 };
 
 // Description of one unit of work: a pair of overlap-save segments of one signal.
@@ -206,22 +211,30 @@ template <class P>
 FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
-  const bool fastA = w.inA >= 0 && w.inA + P::N <= w.x_len;
-  const bool fastB = w.haveB && w.inB >= 0 && w.inB + P::N <= w.x_len;
+  // CTA-uniform: both segments lie entirely inside the signal (no bounds checks needed)
+  const bool fast = w.haveB && w.inA >= 0 && w.inB + P::N <= w.x_len;
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R];
-    static_for<0, R>([&](auto rr) {
-      constexpr int r = decltype(rr)::value;
-      int p = base + r * G::S;
-      float a, b;
-      if (fastA) a = w.x[w.inA + p]; else a = load_x(w.x, w.x_len, w.inA + p);
-      if (fastB) b = w.x[w.inB + p];
-      else b = w.haveB ? load_x(w.x, w.x_len, w.inB + p) : 0.0f;
-      v[bitrev(r, ilog2(R))] = make_float2(a, b);
-    });
+    if (fast) {
+      const float *xa = w.x + (w.inA + base);
+      const float *xb = w.x + (w.inB + base);
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        v[bitrev(r, ilog2(R))] = make_float2(xa[r * G::S], xb[r * G::S]);
+      });
+    } else {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const int p = base + r * G::S;
+        const float a = load_x(w.x, w.x_len, w.inA + p);
+        const float b = w.haveB ? load_x(w.x, w.x_len, w.inB + p) : 0.0f;
+        v[bitrev(r, ilog2(R))] = make_float2(a, b);
+      });
+    }
     dft_inreg<R, false>(v);
     if constexpr (G::S > 1) {
       Powers<R> pw;
@@ -233,7 +246,7 @@ FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
     }
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
-      sm[pad_pos(base + k * G::S)] = v[k];
+      smb[G::off(k)] = v[k];
     });
   });
 }
@@ -247,10 +260,11 @@ FC_HD void fwd_mid(int t, const float2 *tw, float2 *sm) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R];
     static_for<0, R>([&](auto rr) {
       constexpr int r = decltype(rr)::value;
-      v[bitrev(r, ilog2(R))] = sm[pad_pos(base + r * G::S)];
+      v[bitrev(r, ilog2(R))] = smb[G::off(r)];
     });
     dft_inreg<R, false>(v);
     Powers<R> pw;
@@ -261,7 +275,7 @@ FC_HD void fwd_mid(int t, const float2 *tw, float2 *sm) {
     });
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
-      sm[pad_pos(base + k * G::S)] = v[k];
+      smb[G::off(k)] = v[k];
     });
   });
 }
@@ -276,10 +290,11 @@ FC_HD void centre(int t, const float2 *Hperm, float2 *sm) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R], u[R];
     static_for<0, R>([&](auto rr) {
       constexpr int r = decltype(rr)::value;
-      v[bitrev(r, ilog2(R))] = sm[pad_pos(base + r)];
+      v[bitrev(r, ilog2(R))] = smb[G::off(r)];
     });
     dft_inreg<R, false>(v);
     static_for<0, R>([&](auto kk) {
@@ -289,7 +304,7 @@ FC_HD void centre(int t, const float2 *Hperm, float2 *sm) {
     dft_inreg<R, true>(u);
     static_for<0, R>([&](auto rr) {
       constexpr int r = decltype(rr)::value;
-      sm[pad_pos(base + r)] = u[r];
+      smb[G::off(r)] = u[r];
     });
   });
 }
@@ -303,10 +318,11 @@ FC_HD void centre_store_spectrum(int t, float2 *Hperm, float scale, const float2
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R];
     static_for<0, R>([&](auto rr) {
       constexpr int r = decltype(rr)::value;
-      v[bitrev(r, ilog2(R))] = sm[pad_pos(base + r)];
+      v[bitrev(r, ilog2(R))] = smb[G::off(r)];
     });
     dft_inreg<R, false>(v);
     static_for<0, R>([&](auto kk) {
@@ -325,19 +341,20 @@ FC_HD void inv_mid(int t, const float2 *tw, float2 *sm) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R];
     Powers<R> pw;
     pw.init(tw[npp * (P::N / NB)]);
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
-      float2 e = sm[pad_pos(base + k * G::S)];
+      float2 e = smb[G::off(k)];
       if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
       v[bitrev(k, ilog2(R))] = e;
     });
     dft_inreg<R, true>(v);
     static_for<0, R>([&](auto rr) {
       constexpr int r = decltype(rr)::value;
-      sm[pad_pos(base + r * G::S)] = v[r];
+      smb[G::off(r)] = v[r];
     });
   });
 }
@@ -348,42 +365,50 @@ template <class P>
 FC_HD void inv_last(int t, const SegPair &w, const float2 *tw, const float2 *sm) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
+  // CTA-uniform: both segments deliver all N - c_off samples and overwrite
+  const bool fast = !w.accumulate && w.cntA == P::N - w.c_off && w.cntB == w.cntA;
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R];
     if constexpr (G::S > 1) {
       Powers<R> pw;
       pw.init(tw[npp * (P::N / NB)]);
       static_for<0, R>([&](auto kk) {
         constexpr int k = decltype(kk)::value;
-        float2 e = sm[pad_pos(base + k * G::S)];
+        float2 e = smb[G::off(k)];
         if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
         v[bitrev(k, ilog2(R))] = e;
       });
     } else {
       static_for<0, R>([&](auto kk) {
         constexpr int k = decltype(kk)::value;
-        v[bitrev(k, ilog2(R))] = sm[pad_pos(base + k * G::S)];
+        v[bitrev(k, ilog2(R))] = smb[G::off(k)];
       });
     }
     dft_inreg<R, true>(v);
-    static_for<0, R>([&](auto rr) {
-      constexpr int r = decltype(rr)::value;
-      int p = base + r * G::S;          // natural-order circular index
-      int tt = p - w.c_off;
-      if (tt >= 0) {
-        if (tt < w.cntA) {
-          float *o = w.out + (w.outA + tt);
-          *o = w.accumulate ? *o + v[r].x : v[r].x;
+    // natural-order circular index of register r is base + r*S; output index tt = it - c_off
+    const int t0 = base - w.c_off;
+    float *oa = w.out + (w.outA + t0);     // only dereferenced where 0 <= t0 + r*S < cnt
+    float *ob = w.out + (w.outB + t0);
+    if (fast) {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        if (t0 + r * G::S >= 0) {
+          oa[r * G::S] = v[r].x;
+          ob[r * G::S] = v[r].y;
         }
-        if (tt < w.cntB) {
-          float *o = w.out + (w.outB + tt);
-          *o = w.accumulate ? *o + v[r].y : v[r].y;
-        }
-      }
-    });
+      });
+    } else {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const unsigned tt = (unsigned)(t0 + r * G::S);     // negative -> huge
+        if (tt < (unsigned)w.cntA) oa[r * G::S] = w.accumulate ? oa[r * G::S] + v[r].x : v[r].x;
+        if (tt < (unsigned)w.cntB) ob[r * G::S] = w.accumulate ? ob[r * G::S] + v[r].y : v[r].y;
+      });
+    }
   });
 }
 
@@ -398,6 +423,7 @@ FC_HD void spec_first(int t, const float *h, i64 start, int dir, int taps,
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
     G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
     float2 v[R];
     static_for<0, R>([&](auto rr) {
       constexpr int r = decltype(rr)::value;
@@ -416,7 +442,7 @@ FC_HD void spec_first(int t, const float *h, i64 start, int dir, int taps,
     }
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
-      sm[pad_pos(base + k * G::S)] = v[k];
+      smb[G::off(k)] = v[k];
     });
   });
 }
