@@ -52,8 +52,10 @@ static int run_plan(const char *name, int h_len, int x_len, int reverse) {
   std::vector<float2> sm(P::SMEM_FLOAT2), Hperm(P::N);
   i64 start = reverse ? h_len - 1 : 0;
   int dir = reverse ? -1 : 1;
-  for (int t = 0; t < P::T; t++) spec_first<P>(t, h.data(), start, dir, h_len, tw.data(), sm.data());
-  if (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tw.data(), sm.data());
+  std::vector<TwBases<P>> tb(P::T);
+  for (int t = 0; t < P::T; t++) load_twiddle_bases<P>(t, tw.data(), tb[t]);
+  for (int t = 0; t < P::T; t++) spec_first<P>(t, h.data(), start, dir, h_len, tb[t], sm.data());
+  if (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
   for (int t = 0; t < P::T; t++) centre_store_spectrum<P>(t, Hperm.data(), 1.0f / P::N, sm.data());
 
   int out_len = x_len + h_len - 1;
@@ -73,11 +75,16 @@ static int run_plan(const char *name, int h_len, int x_len, int reverse) {
     w.cntB = w.haveB ? (int)(remB < step ? remB : step) : 0;
     w.c_off = h_len - 1;
     w.accumulate = false;
-    for (int t = 0; t < P::T; t++) fwd_first<P>(t, w, tw.data(), sm.data());
-    if (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tw.data(), sm.data());
-    for (int t = 0; t < P::T; t++) centre<P>(t, Hperm.data(), sm.data());
-    if (P::NPASS == 3) for (int t = 0; t < P::T; t++) inv_mid<P>(t, tw.data(), sm.data());
-    for (int t = 0; t < P::T; t++) inv_last<P>(t, w, tw.data(), sm.data());
+    w.dbg = 0;
+    for (int t = 0; t < P::T; t++) fwd_first<P>(t, w, tb[t], sm.data());
+    if (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
+    for (int t = 0; t < P::T; t++) {
+      HRegs<P> hr;
+      load_spectrum<P>(t, Hperm.data(), hr);
+      centre<P>(t, hr, sm.data());
+    }
+    if (P::NPASS == 3) for (int t = 0; t < P::T; t++) inv_mid<P>(t, tb[t], sm.data());
+    for (int t = 0; t < P::T; t++) inv_last<P>(t, w, tb[t], sm.data());
   }
   // double-precision check
   double num = 0, den = 0, maxabs = 0;

@@ -200,15 +200,72 @@ struct SegPair {
   int cntA, cntB;      // number of valid outputs of each segment (<= step), 0 = none
   int c_off;           // first useful circular-convolution sample (h_len - 1 in OS)
   bool accumulate;     // add to out instead of overwriting (partitioned impulse response)
+  int dbg;
 };
 
 FC_HD float load_x(const float *x, i64 x_len, i64 i) {
   return (i >= 0 && i < x_len) ? x[i] : 0.0f;
 }
 
+// Per-thread twiddle bases of the strided passes, loaded once per kernel: the first and
+// last pass share W_N^(n''), the two middle passes share W_NB2^(n'').
+template <class P>
+struct TwBases {
+  float2 w1[P::E / P::R1];
+  float2 w2[P::E / P::R2];
+};
+
+template <class P>
+FC_HD void load_twiddle_bases(int t, const float2 *tw, TwBases<P> &tb) {
+  static_for<0, P::E / P::R1>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    PassGeom<P, P::N, P::R1>::locate(t, j, base, npp, bf);
+    tb.w1[j] = tw[npp];
+  });
+  if constexpr (P::NPASS == 3) {
+    static_for<0, P::E / P::R2>([&](auto jj) {
+      constexpr int j = decltype(jj)::value;
+      int base, npp, bf;
+      PassGeom<P, P::NB2, P::R2>::locate(t, j, base, npp, bf);
+      tb.w2[j] = tw[npp * P::R1];
+    });
+  }
+}
+
+// Filter spectrum in the register order of the centre pass.  Layout of Hperm: the bin held in
+// register k of butterfly j of thread t is Hperm[(k*T + t)*JB + j], JB = E/R3 butterflies per
+// thread, so a thread fetches its JB bins of one k with a single 8*JB-byte load and a warp's
+// loads are contiguous.
+template <class P>
+struct HRegs {
+  float2 h[P::E];      // [j*R3 + k]
+};
+
+template <class P>
+FC_HD void load_spectrum(int t, const float2 *Hperm, HRegs<P> &hr) {
+  constexpr int R = P::R3, JB = P::E / R;
+  static_assert(JB == 1 || JB == 2, "one or two centre butterflies per thread");
+  static_for<0, R>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    if constexpr (JB == 2) {
+#if defined(__CUDA_ARCH__)
+      const float4 q = *reinterpret_cast<const float4 *>(Hperm + (size_t)(k * P::T + t) * 2);
+      hr.h[k] = make_float2(q.x, q.y);
+      hr.h[R + k] = make_float2(q.z, q.w);
+#else
+      hr.h[k] = Hperm[(size_t)(k * P::T + t) * 2];
+      hr.h[R + k] = Hperm[(size_t)(k * P::T + t) * 2 + 1];
+#endif
+    } else {
+      hr.h[k] = Hperm[k * P::T + t];
+    }
+  });
+}
+
 // forward first pass: global -> registers -> R1-point DFT -> twiddle -> shared memory
 template <class P>
-FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
+FC_HD void fwd_first(int t, const SegPair &w, const TwBases<P> &tb, float2 *sm) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
   // CTA-uniform: both segments lie entirely inside the signal (no bounds checks needed)
@@ -219,7 +276,12 @@ FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
     G::locate(t, j, base, npp, bf);
     auto *smb = sm + pad_pos(base);
     float2 v[R];
-    if (fast) {
+    if (w.dbg & 1) {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        v[bitrev(r, ilog2(R))] = make_float2(1.0f + r + t, 2.0f * r - t);
+      });
+    } else if (fast) {
       const float *xa = w.x + (w.inA + base);
       const float *xb = w.x + (w.inB + base);
       static_for<0, R>([&](auto rr) {
@@ -238,7 +300,7 @@ FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
     dft_inreg<R, false>(v);
     if constexpr (G::S > 1) {
       Powers<R> pw;
-      pw.init(tw[npp * (P::N / NB)]);
+      pw.init(tb.w1[j]);
       static_for<1, R>([&](auto kk) {
         constexpr int k = decltype(kk)::value;
         v[k] = cmul(v[k], pw.template get<k>());
@@ -253,7 +315,7 @@ FC_HD void fwd_first(int t, const SegPair &w, const float2 *tw, float2 *sm) {
 
 // forward middle pass (3-pass plans only): shared -> DFT_R2 -> twiddle -> shared (in place)
 template <class P>
-FC_HD void fwd_mid(int t, const float2 *tw, float2 *sm) {
+FC_HD void fwd_mid(int t, const TwBases<P> &tb, float2 *sm) {
   constexpr int R = P::R2, NB = P::NB2;
   using G = PassGeom<P, NB, R>;
   static_for<0, P::E / R>([&](auto jj) {
@@ -268,7 +330,7 @@ FC_HD void fwd_mid(int t, const float2 *tw, float2 *sm) {
     });
     dft_inreg<R, false>(v);
     Powers<R> pw;
-    pw.init(tw[npp * (P::N / NB)]);
+    pw.init(tb.w2[j]);
     static_for<1, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
       v[k] = cmul(v[k], pw.template get<k>());
@@ -280,11 +342,12 @@ FC_HD void fwd_mid(int t, const float2 *tw, float2 *sm) {
   });
 }
 
-// centre: last forward pass, pointwise product with the filter spectrum, first inverse pass.
-// Hperm layout: bin held in register k of butterfly bf is Hperm[k * NBF3 + bf].
+// centre: last forward pass, pointwise product with the filter spectrum (already in
+// registers, see load_spectrum), first inverse pass.
 template <class P>
-FC_HD void centre(int t, const float2 *Hperm, float2 *sm) {
+FC_HD void centre(int t, const HRegs<P> &hr, float2 *sm) {
   constexpr int R = P::R3;
+  static_assert(R == 16, "contiguous pass assumes 16-slot padded rows");
   using G = PassGeom<P, R, R>;
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
@@ -299,7 +362,7 @@ FC_HD void centre(int t, const float2 *Hperm, float2 *sm) {
     dft_inreg<R, false>(v);
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
-      u[bitrev(k, ilog2(R))] = cmul(v[k], Hperm[k * P::NBF3 + bf]);
+      u[bitrev(k, ilog2(R))] = cmul(v[k], hr.h[j * R + k]);
     });
     dft_inreg<R, true>(u);
     static_for<0, R>([&](auto rr) {
@@ -327,14 +390,14 @@ FC_HD void centre_store_spectrum(int t, float2 *Hperm, float scale, const float2
     dft_inreg<R, false>(v);
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
-      Hperm[k * P::NBF3 + bf] = make_float2(v[k].x * scale, v[k].y * scale);
+      Hperm[(size_t)(k * P::T + t) * (P::E / R) + j] = make_float2(v[k].x * scale, v[k].y * scale);
     });
   });
 }
 
 // inverse middle pass (3-pass plans only): shared -> conj twiddle -> IDFT_R2 -> shared
 template <class P>
-FC_HD void inv_mid(int t, const float2 *tw, float2 *sm) {
+FC_HD void inv_mid(int t, const TwBases<P> &tb, float2 *sm) {
   constexpr int R = P::R2, NB = P::NB2;
   using G = PassGeom<P, NB, R>;
   static_for<0, P::E / R>([&](auto jj) {
@@ -344,7 +407,7 @@ FC_HD void inv_mid(int t, const float2 *tw, float2 *sm) {
     auto *smb = sm + pad_pos(base);
     float2 v[R];
     Powers<R> pw;
-    pw.init(tw[npp * (P::N / NB)]);
+    pw.init(tb.w2[j]);
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
       float2 e = smb[G::off(k)];
@@ -362,7 +425,7 @@ FC_HD void inv_mid(int t, const float2 *tw, float2 *sm) {
 // inverse last pass: shared -> conj twiddle -> IDFT_R1 -> global (real part -> segment A,
 // imaginary part -> segment B), keeping only circular samples >= c_off.
 template <class P>
-FC_HD void inv_last(int t, const SegPair &w, const float2 *tw, const float2 *sm) {
+FC_HD void inv_last(int t, const SegPair &w, const TwBases<P> &tb, const float2 *sm) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
   // CTA-uniform: both segments deliver all N - c_off samples and overwrite
@@ -375,7 +438,7 @@ FC_HD void inv_last(int t, const SegPair &w, const float2 *tw, const float2 *sm)
     float2 v[R];
     if constexpr (G::S > 1) {
       Powers<R> pw;
-      pw.init(tw[npp * (P::N / NB)]);
+      pw.init(tb.w1[j]);
       static_for<0, R>([&](auto kk) {
         constexpr int k = decltype(kk)::value;
         float2 e = smb[G::off(k)];
@@ -393,7 +456,11 @@ FC_HD void inv_last(int t, const SegPair &w, const float2 *tw, const float2 *sm)
     const int t0 = base - w.c_off;
     float *oa = w.out + (w.outA + t0);     // only dereferenced where 0 <= t0 + r*S < cnt
     float *ob = w.out + (w.outB + t0);
-    if (fast) {
+    if (w.dbg & 2) {
+      float acc = 0;
+      static_for<0, R>([&](auto rr) { acc += v[decltype(rr)::value].x + v[decltype(rr)::value].y; });
+      if (acc == 123.456f) oa[0] = acc;
+    } else if (fast) {
       static_for<0, R>([&](auto rr) {
         constexpr int r = decltype(rr)::value;
         if (t0 + r * G::S >= 0) {
@@ -416,7 +483,7 @@ FC_HD void inv_last(int t, const SegPair &w, const float2 *tw, const float2 *sm)
 // (m < taps) -> registers -> DFT -> twiddle -> shared.
 template <class P>
 FC_HD void spec_first(int t, const float *h, i64 start, int dir, int taps,
-                      const float2 *tw, float2 *sm) {
+                      const TwBases<P> &tb, float2 *sm) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
   static_for<0, P::E / R>([&](auto jj) {
@@ -434,7 +501,7 @@ FC_HD void spec_first(int t, const float *h, i64 start, int dir, int taps,
     dft_inreg<R, false>(v);
     if constexpr (G::S > 1) {
       Powers<R> pw;
-      pw.init(tw[npp * (P::N / NB)]);
+      pw.init(tb.w1[j]);
       static_for<1, R>([&](auto kk) {
         constexpr int k = decltype(kk)::value;
         v[k] = cmul(v[k], pw.template get<k>());

@@ -43,6 +43,8 @@ struct OsParams {
   i64 npairs;               // segment pairs per signal
   i64 total;                // npairs * batch
   int accumulate;
+  int dbg;
+  i64 prefetch_distance;    // work items between a CTA and its successor on the same SM
 };
 
 struct SpecParams {
@@ -70,10 +72,12 @@ __global__ void __launch_bounds__(P::T) os_spectrum_kernel(SpecParams p) {
   int dir;
   if (p.reverse) { start = j0 + taps - 1; dir = -1; }
   else { start = p.h_len - j0 - taps; dir = 1; }
-  spec_first<P>(t, p.h, start, dir, taps, p.tw, sm);
+  TwBases<P> tb;
+  load_twiddle_bases<P>(t, p.tw, tb);
+  spec_first<P>(t, p.h, start, dir, taps, tb, sm);
   __syncthreads();
   if constexpr (P::NPASS == 3) {
-    fwd_mid<P>(t, p.tw, sm);
+    fwd_mid<P>(t, tb, sm);
     __syncthreads();
   }
   centre_store_spectrum<P>(t, p.spectrum + (size_t)part * P::N, p.scale, sm);
@@ -89,7 +93,30 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
   const i64 item = (i64)blockIdx.x * G + grp;
   const bool live = item < p.total;     // whole group idles (but still hits the barriers)
   SegPair w;
+  TwBases<P> tb;
+  HRegs<P> hr;
+  if (t == 0) {
+    // Pull the input of the CTA that will follow this one on the SM into L2 while this CTA
+    // computes (CTAs are dispatched in index order, one wave = p.prefetch_distance items).
+    const i64 nxt = item + p.prefetch_distance;
+    if (p.prefetch_distance > 0 && nxt < p.total) {
+      const i64 nb = nxt / p.npairs;
+      const i64 nsa = (nxt % p.npairs) * 2;
+      i64 lo = nsa * p.step + p.in_shift;
+      i64 hi = lo + p.step + P::N;
+      if (lo < 0) lo = 0;
+      if (hi > p.x_len) hi = p.x_len;
+      const float *base = p.x + nb * p.x_stride;
+      unsigned long long a0 = ((unsigned long long)(base + lo) + 15ull) & ~15ull;
+      unsigned long long a1 = (unsigned long long)(base + hi) & ~15ull;
+      if (a1 > a0) {
+        unsigned bytes = (unsigned)(a1 - a0);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(bytes) : "memory");
+      }
+    }
+  }
   if (live) {
+    load_twiddle_bases<P>(t, p.tw, tb);
     const i64 b = item / p.npairs;
     const i64 sa = (item % p.npairs) * 2;
     w.x = p.x + b * p.x_stride;
@@ -105,20 +132,23 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     w.cntB = w.haveB ? (int)(remB < p.step ? remB : p.step) : 0;
     w.c_off = p.c_off;
     w.accumulate = p.accumulate != 0;
-    fwd_first<P>(t, w, p.tw, sm);
+    w.dbg = p.dbg;
+    fwd_first<P>(t, w, tb, sm);
   }
+  if constexpr (P::NPASS == 3) {
+    __syncthreads();
+    if (live) fwd_mid<P>(t, tb, sm);
+  }
+  // the filter spectrum does not depend on shared memory: fetch it across the barrier
+  if (live) load_spectrum<P>(t, p.spectrum, hr);
+  __syncthreads();
+  if (live) centre<P>(t, hr, sm);
   __syncthreads();
   if constexpr (P::NPASS == 3) {
-    if (live) fwd_mid<P>(t, p.tw, sm);
+    if (live) inv_mid<P>(t, tb, sm);
     __syncthreads();
   }
-  if (live) centre<P>(t, p.spectrum, sm);
-  __syncthreads();
-  if constexpr (P::NPASS == 3) {
-    if (live) inv_mid<P>(t, p.tw, sm);
-    __syncthreads();
-  }
-  if (live) inv_last<P>(t, w, p.tw, sm);
+  if (live) inv_last<P>(t, w, tb, sm);
 }
 
 // ---- plan table ---------------------------------------------------------------------------
@@ -145,7 +175,20 @@ void launch_fused(const OsParams &p, cudaStream_t stream) {
   i64 blocks = (p.total + G - 1) / G;
   B200_REQUIRE(blocks < 2147483647LL, "overlap-save grid too large");
   b200_prof_begin(B200_PROF_FUSED, stream);
-  os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(p);
+  OsParams q = p;
+  {
+    // resident CTAs per wave = SMs x CTAs per SM (by shared memory; registers allow as many)
+    static int wave[16] = {0};
+    if (dev < 16 && wave[dev] == 0) {
+      int per_sm = 0, sms = 0;
+      B200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, os_fused_kernel<P, G>,
+                                                                    P::T * G, smem));
+      B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      wave[dev] = per_sm * sms > 0 ? per_sm * sms : 1;
+    }
+    q.prefetch_distance = getenv("B200_NO_PREFETCH") ? 0 : (i64)(dev < 16 ? wave[dev] : 148) * G;
+  }
+  os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(q);
   b200_prof_end(B200_PROF_FUSED, stream);
   B200_CUDA_CHECK(cudaGetLastError());
   b200_count_launch(1);
@@ -215,6 +258,7 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
   op.x = job.x; op.x_len = job.x_len; op.x_stride = job.x_stride;
   op.out = job.out; op.out_len = job.out_len; op.out_stride = job.out_stride;
   op.tw = tw;
+  op.dbg = getenv("B200_DBG") ? atoi(getenv("B200_DBG")) : 0;
 
 #define B200_DISPATCH(PLAN, GROUPS)                                                    \
   case PLAN::N: {                                                                      \

@@ -11,6 +11,7 @@
  */
 #define LIBSIMD_IMPLEMENTATION
 #include <simd/b200.h>
+#include <stdlib.h>
 #include "../csrc/b200_internal.h"
 
 /* Direct kernel wins while the impulse response is short (FP32-bound at 2*h FLOP/output,
@@ -33,6 +34,7 @@ ConvolutionAlgorithm simd_b200_select_algorithm(size_t x_length, size_t h_length
  * impulse responses that would leave less than half a transform of useful output are
  * split into partitions of N/2 taps. */
 int b200_os_pick_n(long long h_len, long long out_len) {
+  if (getenv("B200_FORCE_N")) return atoi(getenv("B200_FORCE_N"));
   int best = B200_FFT_MAX;
   double best_cost = 1e300;
   for (int n = B200_FFT_MIN; n <= B200_FFT_MAX; n *= 2) {
