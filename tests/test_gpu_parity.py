@@ -277,6 +277,37 @@ def test_filter_shard_reassembles_long_signal(simd, oracle):
     assert rel_l2(d, second[:5000]) < 5e-6
 
 
+def test_host_pointer_pipeline_batches_and_long_signals(simd, oracle):
+    """Host buffers flow through the two-slot H2D / kernel / D2H pipeline: a batch is cut
+    into groups of signals, one long signal into time slices with halo.  Results must equal
+    the device-pointer path bit for bit (same kernels) and the oracle within tolerance."""
+    import torch
+    simd.use_torch_stream()
+    for B, xl, hl in [(40, 70000, 64), (24, 300000, 3000)]:
+        x, h = uni(B, B, xl), uni(hl, hl)
+        with simd.Handle(xl, hl) as hd:
+            host = hd(x, h)
+            dev = hd(torch.from_numpy(x).cuda(), torch.from_numpy(h).cuda())
+            torch.cuda.synchronize()
+        assert np.array_equal(host, dev.cpu().numpy())
+        for b in (0, B - 1):
+            check(host[b], oracle.convolve_fft(x[b], h, 0), x[b], h, f"pipeline batch row {b}")
+    for xl, hl, corr in [(20_000_000, 100, False), (18_000_000, 5000, True)]:
+        x, h = uni(xl % 1000, xl), uni(hl, hl)
+        with simd.Handle(xl, hl, "", corr) as hd:
+            host = hd(x, h)
+            dev = hd(torch.from_numpy(x).cuda(), torch.from_numpy(h).cuda())
+            torch.cuda.synchronize()
+        d = dev.cpu().numpy()
+        assert rel_l2(host, d) < 2e-6      # slices may pick another transform length
+        for n0 in (0, 8 * 2 ** 20 - 2000, xl - 3000):
+            lo = max(0, n0 - (hl - 1))
+            want = oracle.convolve_f64(x[lo:n0 + 4000], h, corr)[n0 - lo:n0 - lo + 4000]
+            got = host[n0:n0 + 4000]
+            ok, r, m = parity_ok(got, want[:got.size], x[lo:n0 + 4000], h)
+            assert ok, (xl, hl, n0, r, m)
+
+
 def test_kernel_launch_counter(simd):
     before = simd.lib.simd_b200_kernel_launches()
     simd.convolve_simd(KAT_X, KAT_H)

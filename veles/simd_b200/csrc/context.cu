@@ -16,14 +16,21 @@ namespace {
 
 constexpr int kMaxDev = 16;
 
-struct Staging {        // grow-only device + pinned-free staging for host-pointer callers
-  float *x = nullptr, *h = nullptr, *out = nullptr;
-  size_t x_cap = 0, h_cap = 0, out_cap = 0;
+struct Staging {        // grow-only device staging for host-pointer callers (two slots)
+  float *x[2] = {nullptr, nullptr}, *out[2] = {nullptr, nullptr}, *h = nullptr;
+  size_t x_cap[2] = {0, 0}, out_cap[2] = {0, 0}, h_cap = 0;
+};
+
+struct Pipe {           // copy streams / events of the host-pointer pipeline
+  bool ready = false;
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2], ev_comp[2], ev_out[2], ev_h;
 };
 
 struct DeviceCtx {
   cudaStream_t own_stream = nullptr;   // created lazily, non-blocking
   Staging staging;                     // used by handle-less calls (convolve_simd, ...)
+  Pipe pipe;
   float2 *spectrum = nullptr;          // scratch for handle-less FFT jobs
   size_t spectrum_cap = 0;
 };
@@ -173,9 +180,13 @@ extern "C" B200Plan *b200_plan_create(int algorithm, long long x_len, long long 
   B200_CUDA_CHECK(cudaMalloc(&plan->os.spectrum,
                              sizeof(float2) * (size_t)n_fft * plan->os.max_parts));
   // staging for host-pointer callers is sized now so the call path does not allocate
-  grow(&plan->staging.x, &plan->staging.x_cap, (size_t)x_len);
-  grow(&plan->staging.h, &plan->staging.h_cap, (size_t)h_len);
-  grow(&plan->staging.out, &plan->staging.out_cap, (size_t)(x_len + h_len - 1));
+  {
+    const size_t cap = (size_t)16 << 20;     // one pipeline piece at most (see b200_run)
+    size_t xs = (size_t)x_len, os = (size_t)(x_len + h_len - 1);
+    grow(&plan->staging.x[0], &plan->staging.x_cap[0], xs < cap ? xs : cap);
+    grow(&plan->staging.out[0], &plan->staging.out_cap[0], os < cap ? os : cap);
+    grow(&plan->staging.h, &plan->staging.h_cap, (size_t)h_len);
+  }
   return plan;
 }
 
@@ -187,9 +198,11 @@ extern "C" void b200_plan_destroy(B200Plan *plan) {
   // outstanding asynchronous work may still read the spectrum / staging buffers
   B200_CUDA_CHECK(cudaDeviceSynchronize());
   cudaFree(plan->os.spectrum);
-  cudaFree(plan->staging.x);
+  for (int sl = 0; sl < 2; sl++) {
+    cudaFree(plan->staging.x[sl]);
+    cudaFree(plan->staging.out[sl]);
+  }
   cudaFree(plan->staging.h);
-  cudaFree(plan->staging.out);
   if (prev != plan->device) B200_CUDA_CHECK(cudaSetDevice(prev));
   plan->magic = 0;
   delete plan;
@@ -197,7 +210,7 @@ extern "C" void b200_plan_destroy(B200Plan *plan) {
 
 extern "C" int b200_plan_n_fft(const B200Plan *plan) { return plan->os.n_fft; }
 extern "C" float *b200_plan_spectrum(const B200Plan *plan) { return (float *)plan->os.spectrum; }
-extern "C" float *b200_plan_scratch(const B200Plan *plan) { return plan->staging.x; }
+extern "C" float *b200_plan_scratch(const B200Plan *plan) { return plan->staging.x[0]; }
 
 namespace {
 
@@ -262,6 +275,10 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
   }
 
   // ---- host-pointer path: stage, run, copy back, synchronise --------------------------
+  // The job is cut into pieces (groups of whole signals, or -- for one long signal -- time
+  // slices with their (h-1)-sample halo) that flow through two staging slots on three
+  // streams, so the H2D copy of piece i+1, the kernels of piece i and the D2H copy of piece
+  // i-1 overlap (PCIe is full duplex).
   std::unique_lock<std::mutex> plan_lock, ctx_lock;
   Staging *st;
   if (plan) {
@@ -273,56 +290,116 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     ctx_lock = std::unique_lock<std::mutex>(staged_call_mu);
     st = &g_ctx[dev].staging;
   }
-  // Batches are processed in chunks so that staging stays bounded and copies overlap
-  // poorly only for the first/last chunk (copy-in of chunk i+1 queues behind compute of i
-  // on the same stream; a second stream would add overlap -- see DESIGN.md).
-  const size_t x_row = (size_t)job->x_len, o_row = (size_t)job->out_len;
-  const size_t budget = (size_t)64 << 20;        // floats per staging buffer (256 MiB)
-  i64 chunk = (i64)(budget / (x_row > o_row ? x_row : o_row));
-  if (chunk < 1) chunk = 1;
-  if (chunk > job->batch) chunk = job->batch;
-  if (!xd) grow(&st->x, &st->x_cap, x_row * (size_t)chunk);
-  if (!hd) grow(&st->h, &st->h_cap, (size_t)job->h_len);
-  if (!od) grow(&st->out, &st->out_cap, o_row * (size_t)chunk);
+  Pipe &pipe = g_ctx[dev].pipe;
+  {
+    std::lock_guard<std::mutex> lock(g_mu);
+    if (!pipe.ready) {
+      B200_CUDA_CHECK(cudaStreamCreateWithFlags(&pipe.s_in, cudaStreamNonBlocking));
+      B200_CUDA_CHECK(cudaStreamCreateWithFlags(&pipe.s_out, cudaStreamNonBlocking));
+      for (int i = 0; i < 2; i++) {
+        B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_in[i], cudaEventDisableTiming));
+        B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_comp[i], cudaEventDisableTiming));
+        B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_out[i], cudaEventDisableTiming));
+      }
+      B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_h, cudaEventDisableTiming));
+      pipe.ready = true;
+    }
+  }
 
+  const i64 x_row = job->x_len, o_row = job->out_len;
+  const i64 budget = (i64)16 << 20;              // floats per staging buffer (64 MiB)
+  const bool slice_time = job->batch == 1 && o_row > budget;
+  i64 rows_per_piece = 1, outs_per_piece = o_row;
+  if (slice_time) {
+    outs_per_piece = budget / 2;
+  } else {
+    rows_per_piece = budget / (x_row > o_row ? x_row : o_row);
+    if (rows_per_piece < 1) rows_per_piece = 1;
+    if (rows_per_piece > job->batch) rows_per_piece = job->batch;
+    // at least ~8 pieces when the batch allows, so the pipeline has something to overlap
+    if (job->batch >= 16 && rows_per_piece > job->batch / 8) rows_per_piece = job->batch / 8;
+  }
+  const i64 piece_x = slice_time ? outs_per_piece + job->h_len : rows_per_piece * x_row;
+  const i64 piece_o = slice_time ? outs_per_piece : rows_per_piece * o_row;
+  const i64 n_pieces = slice_time ? (o_row + outs_per_piece - 1) / outs_per_piece
+                                  : (job->batch + rows_per_piece - 1) / rows_per_piece;
+  for (int sl = 0; sl < (n_pieces > 1 ? 2 : 1); sl++) {
+    if (!xd) grow(&st->x[sl], &st->x_cap[sl], (size_t)piece_x);
+    if (!od) grow(&st->out[sl], &st->out_cap[sl], (size_t)piece_o);
+  }
   if (!hd) {
+    grow(&st->h, &st->h_cap, (size_t)job->h_len);
     B200_CUDA_CHECK(cudaMemcpyAsync(st->h, job->h, sizeof(float) * job->h_len,
                                     cudaMemcpyHostToDevice, stream));
     dj.h = st->h;
   }
-  for (i64 b0 = 0; b0 < job->batch; b0 += chunk) {
-    const i64 nb = (job->batch - b0) < chunk ? (job->batch - b0) : chunk;
-    dj.batch = nb;
-    if (!xd) {
-      if (nb == 1 || job->x_stride == (i64)x_row) {   // contiguous: no 2-D pitch limit
-        B200_CUDA_CHECK(cudaMemcpyAsync(st->x, job->x + b0 * job->x_stride,
-                                        sizeof(float) * x_row * (size_t)nb,
-                                        cudaMemcpyHostToDevice, stream));
-      } else {
-        B200_CUDA_CHECK(cudaMemcpy2DAsync(st->x, sizeof(float) * x_row,
-                                          job->x + b0 * job->x_stride,
-                                          sizeof(float) * job->x_stride, sizeof(float) * x_row,
-                                          (size_t)nb, cudaMemcpyHostToDevice, stream));
-      }
-      dj.x = st->x; dj.x_stride = (i64)x_row;
+
+  for (i64 pi = 0; pi < n_pieces; pi++) {
+    const int sl = (int)(pi & 1);
+    // --- describe the piece ---------------------------------------------------------------
+    const float *src_x; float *dst_o;
+    i64 px_len, po_len, p_rows, p_pad;
+    if (slice_time) {
+      const i64 o0 = pi * outs_per_piece;
+      const i64 o1 = o0 + outs_per_piece < o_row ? o0 + outs_per_piece : o_row;
+      i64 lo = o0 - job->pad; if (lo < 0) lo = 0;
+      i64 hi = o1 - job->pad + job->h_len - 1; if (hi > x_row) hi = x_row;
+      if (hi < lo) hi = lo;
+      src_x = job->x + lo; px_len = hi - lo; p_pad = job->pad - o0 + lo;
+      dst_o = job->out + o0; po_len = o1 - o0; p_rows = 1;
     } else {
-      dj.x = job->x + b0 * job->x_stride;
+      const i64 b0 = pi * rows_per_piece;
+      p_rows = (job->batch - b0) < rows_per_piece ? (job->batch - b0) : rows_per_piece;
+      src_x = job->x + b0 * job->x_stride; px_len = x_row; p_pad = job->pad;
+      dst_o = job->out + b0 * job->out_stride; po_len = o_row;
     }
-    if (!od) { dj.out = st->out; dj.out_stride = (i64)o_row; }
-    else dj.out = job->out + b0 * job->out_stride;
-    launch_device_job(plan, algorithm, dj, stream);
-    if (!od) {
-      if (nb == 1 || job->out_stride == (i64)o_row) {
-        B200_CUDA_CHECK(cudaMemcpyAsync(job->out + b0 * job->out_stride, st->out,
-                                        sizeof(float) * o_row * (size_t)nb,
-                                        cudaMemcpyDeviceToHost, stream));
-      } else {
-        B200_CUDA_CHECK(cudaMemcpy2DAsync(job->out + b0 * job->out_stride,
-                                          sizeof(float) * job->out_stride, st->out,
-                                          sizeof(float) * o_row, sizeof(float) * o_row,
-                                          (size_t)nb, cudaMemcpyDeviceToHost, stream));
+    dj.batch = p_rows; dj.x_len = px_len; dj.out_len = po_len; dj.pad = p_pad;
+    // --- H2D ------------------------------------------------------------------------------
+    if (!xd) {
+      if (pi >= 2) B200_CUDA_CHECK(cudaStreamWaitEvent(pipe.s_in, pipe.ev_comp[sl], 0));
+      if (px_len > 0) {
+        if (p_rows == 1 || job->x_stride == px_len) {   // contiguous: no 2-D pitch limit
+          B200_CUDA_CHECK(cudaMemcpyAsync(st->x[sl], src_x, sizeof(float) * px_len * p_rows,
+                                          cudaMemcpyHostToDevice, pipe.s_in));
+        } else {
+          B200_CUDA_CHECK(cudaMemcpy2DAsync(st->x[sl], sizeof(float) * px_len, src_x,
+                                            sizeof(float) * job->x_stride, sizeof(float) * px_len,
+                                            (size_t)p_rows, cudaMemcpyHostToDevice, pipe.s_in));
+        }
       }
+      B200_CUDA_CHECK(cudaEventRecord(pipe.ev_in[sl], pipe.s_in));
+      B200_CUDA_CHECK(cudaStreamWaitEvent(stream, pipe.ev_in[sl], 0));
+      dj.x = st->x[sl]; dj.x_stride = px_len;
+    } else {
+      dj.x = src_x; dj.x_stride = job->x_stride;
+    }
+    // --- kernels --------------------------------------------------------------------------
+    if (!od) {
+      if (pi >= 2) B200_CUDA_CHECK(cudaStreamWaitEvent(stream, pipe.ev_out[sl], 0));
+      dj.out = st->out[sl]; dj.out_stride = po_len;
+    } else {
+      dj.out = dst_o; dj.out_stride = job->out_stride;
+    }
+    if (px_len > 0) {
+      launch_device_job(plan, algorithm, dj, stream);
+    } else {
+      B200_CUDA_CHECK(cudaMemsetAsync(dj.out, 0, sizeof(float) * po_len, stream));
+    }
+    B200_CUDA_CHECK(cudaEventRecord(pipe.ev_comp[sl], stream));
+    // --- D2H ------------------------------------------------------------------------------
+    if (!od) {
+      B200_CUDA_CHECK(cudaStreamWaitEvent(pipe.s_out, pipe.ev_comp[sl], 0));
+      if (p_rows == 1 || job->out_stride == po_len) {
+        B200_CUDA_CHECK(cudaMemcpyAsync(dst_o, st->out[sl], sizeof(float) * po_len * p_rows,
+                                        cudaMemcpyDeviceToHost, pipe.s_out));
+      } else {
+        B200_CUDA_CHECK(cudaMemcpy2DAsync(dst_o, sizeof(float) * job->out_stride, st->out[sl],
+                                          sizeof(float) * po_len, sizeof(float) * po_len,
+                                          (size_t)p_rows, cudaMemcpyDeviceToHost, pipe.s_out));
+      }
+      B200_CUDA_CHECK(cudaEventRecord(pipe.ev_out[sl], pipe.s_out));
     }
   }
+  if (!od) B200_CUDA_CHECK(cudaStreamSynchronize(pipe.s_out));
   B200_CUDA_CHECK(cudaStreamSynchronize(stream));
 }

@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
   extern __shared__ float4 smem4[];
   float *gs = reinterpret_cast<float *>(smem4);          // hc_max + 16 taps
   float *xbuf0 = gs + p.hc_max + 16;                     // two padded x windows
+  float *obuf = xbuf0 + 2 * p.xbuf_floats;               // padded output tile
 
   const int tid = threadIdx.x;
   const i64 b = blockIdx.x / p.strips_per_signal;
@@ -131,16 +132,20 @@ __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
 
   auto stage = [&](i64 tile, float *xs) {
     const i64 xi0 = tile * kTile - p.pad;
-    const float *src = xb + xi0;
+    const float *s = xb + xi0 + tid;
+    // q advances by kTPB = 128 (a multiple of the 16-float row), so the padded address
+    // advances by a constant 128 + 32 floats: no per-element index arithmetic
+    float *d = xs + padx(tid);
+    const int iters = (wlen - tid + kTPB - 1) / kTPB;
     if (xi0 >= 0 && xi0 + wlen <= p.x_len) {
 #pragma unroll 4
-      for (int q = tid; q < wlen; q += kTPB) cp_async4(xs + padx(q), src + q, true);
+      for (int k = 0; k < iters; k++, d += kTPB + kTPB / 4, s += kTPB) cp_async4(d, s, true);
     } else {
+      i64 i = xi0 + tid;
 #pragma unroll 2
-      for (int q = tid; q < wlen; q += kTPB) {
-        const i64 i = xi0 + q;
+      for (int k = 0; k < iters; k++, d += kTPB + kTPB / 4, s += kTPB, i += kTPB) {
         const bool ok = i >= 0 && i < p.x_len;
-        cp_async4(xs + padx(q), ok ? src + q : xb, ok);
+        cp_async4(d, ok ? s : xb, ok);
       }
     }
     cp_async_commit();
@@ -166,10 +171,10 @@ __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
     for (int r = 0; r < kR; r++) acc[r] = 0.f;
     if (active) accumulate_taps(acc, gs, xs + padx(t0), hc);
 
-    // results -> shared (same padded rows) -> coalesced global stores
-    __syncthreads();
+    // results -> their own shared region (padded rows; last read before this iteration's
+    // top barrier) -> coalesced global stores
     if (active) {
-      float *orow = xs + padx(t0);
+      float *orow = obuf + padx(t0);
 #pragma unroll
       for (int i = 0; i < 4; i++) {
         *reinterpret_cast<float4 *>(orow + 4 * i) =
@@ -177,9 +182,11 @@ __global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
       }
     }
     __syncthreads();
-    float *o = ob + n0;
+    float *o = ob + n0 + tid;
+    const float *sr = obuf + padx(tid);
+    const int oiters = (cnt - tid + kTPB - 1) / kTPB;
 #pragma unroll 4
-    for (int i = tid; i < cnt; i += kTPB) o[i] = xs[padx(i)];
+    for (int k = 0; k < oiters; k++, o += kTPB, sr += kTPB + kTPB / 4) *o = *sr;
   }
 }
 
@@ -262,7 +269,7 @@ void b200_direct_launch(const DevJob &job, cudaStream_t stream) {
     p.strips_per_signal = (p.tiles_per_signal + strip - 1) / strip;
     const i64 blocks = p.strips_per_signal * job.batch;
     B200_REQUIRE(blocks < 2147483647LL, "direct kernel grid too large");
-    size_t smem = sizeof(float) * (size_t)(p.hc_max + 16 + 2 * p.xbuf_floats);
+    size_t smem = sizeof(float) * (size_t)(p.hc_max + 16 + 2 * p.xbuf_floats + (kTile / 16 + 1) * 20);
     direct_kernel<<<(unsigned)blocks, kTPB, smem, stream>>>(p);
   } else {
     p.strip = 1;
