@@ -223,6 +223,8 @@ def main():
     op, batch, x_len, h_len, desc = WORKLOADS[args.workload]
     corr = op == "correlate"
     out_len = x_len + h_len - 1
+    if args.workload == "c5" and world > 1:
+        return run_sharded_long_signal(args, v, world, rank, local)
     g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
     x = torch.rand((batch, x_len), generator=g, device="cuda") * 2 - 1
     h = torch.rand((h_len,), generator=g, device="cuda") * 2 - 1
@@ -365,6 +367,55 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_sharded_long_signal(args, v, world, rank, local):
+    """C5 on N GPUs: the 2^30-sample signal is pre-sharded (contiguous, device resident);
+    each step = the (h-1)-sample halo exchange (NCCL send/recv) + the shard kernels.
+    Total work is fixed, so this line reports strong scaling."""
+    import torch
+    import torch.distributed as dist
+    from veles.simd_b200 import sharded
+    op, batch, x_len, h_len, desc = WORKLOADS["c5"]
+    s0, e0 = sharded.signal_range(x_len, rank, world)
+    ext, x_local = sharded.alloc_shard(e0 - s0, h_len - 1, device="cuda")
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
+    x_local.copy_(torch.rand((e0 - s0,), generator=g, device="cuda") * 2 - 1)
+    gh = torch.Generator(device="cuda").manual_seed(0xC0FFEE)
+    h = torch.rand((h_len,), generator=gh, device="cuda") * 2 - 1
+    n_out = (e0 - s0) + (h_len - 1 if rank == world - 1 else 0)
+    y = torch.empty((n_out,), device="cuda")
+
+    def compute(x, hh, reverse, left_pad, result_length):
+        return v.filter_shard(x, hh, reverse, left_pad, result_length, out=y)
+
+    def step():
+        sharded.filter_long_signal(x_local, h, x_len, rank, world, compute, ext=ext)
+
+    for _ in range(args.warmup):
+        step()
+    dist.barrier(); torch.cuda.synchronize()
+    launches0 = v.lib.simd_b200_kernel_launches()
+    e0_, e1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0_.record()
+    for _ in range(args.steps):
+        step()
+    e1_.record()
+    dist.barrier(); torch.cuda.synchronize()
+    t = torch.tensor([e0_.elapsed_time(e1_)], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = t.item() / args.steps
+    if rank == 0:
+        line = {"metric": "conv1d_output_gsamples_per_s", "value": (x_len + h_len - 1) / (ms * 1e-3) / 1e9,
+                "unit": "GSamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"c5: {desc}", "sharding": "contiguous shards + (h-1) halo via NCCL send/recv",
+                           "l2": "inputs larger than L2"},
+                "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0),
+                "e2e": None, "roofline": None, "cpu_baseline": None, "clocks": None}
+        print(json.dumps(line), flush=True)
+    dist.destroy_process_group()
 
 
 class ForcedHandle:
