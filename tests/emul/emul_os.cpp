@@ -75,7 +75,6 @@ static int run_plan(const char *name, int h_len, int x_len, int reverse) {
     w.cntB = w.haveB ? (int)(remB < step ? remB : step) : 0;
     w.c_off = h_len - 1;
     w.accumulate = false;
-    w.dbg = 0;
     for (int t = 0; t < P::T; t++) fwd_first<P>(t, w, tb[t], sm.data());
     if (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
     for (int t = 0; t < P::T; t++) {

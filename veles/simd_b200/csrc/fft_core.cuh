@@ -200,7 +200,6 @@ struct SegPair {
   int cntA, cntB;      // number of valid outputs of each segment (<= step), 0 = none
   int c_off;           // first useful circular-convolution sample (h_len - 1 in OS)
   bool accumulate;     // add to out instead of overwriting (partitioned impulse response)
-  int dbg;
 };
 
 FC_HD float load_x(const float *x, i64 x_len, i64 i) {
@@ -276,12 +275,7 @@ FC_HD void fwd_first(int t, const SegPair &w, const TwBases<P> &tb, float2 *sm) 
     G::locate(t, j, base, npp, bf);
     auto *smb = sm + pad_pos(base);
     float2 v[R];
-    if (w.dbg & 1) {
-      static_for<0, R>([&](auto rr) {
-        constexpr int r = decltype(rr)::value;
-        v[bitrev(r, ilog2(R))] = make_float2(1.0f + r + t, 2.0f * r - t);
-      });
-    } else if (fast) {
+    if (fast) {
       const float *xa = w.x + (w.inA + base);
       const float *xb = w.x + (w.inB + base);
       static_for<0, R>([&](auto rr) {
@@ -456,11 +450,7 @@ FC_HD void inv_last(int t, const SegPair &w, const TwBases<P> &tb, const float2 
     const int t0 = base - w.c_off;
     float *oa = w.out + (w.outA + t0);     // only dereferenced where 0 <= t0 + r*S < cnt
     float *ob = w.out + (w.outB + t0);
-    if (w.dbg & 2) {
-      float acc = 0;
-      static_for<0, R>([&](auto rr) { acc += v[decltype(rr)::value].x + v[decltype(rr)::value].y; });
-      if (acc == 123.456f) oa[0] = acc;
-    } else if (fast) {
+    if (fast) {
       static_for<0, R>([&](auto rr) {
         constexpr int r = decltype(rr)::value;
         if (t0 + r * G::S >= 0) {

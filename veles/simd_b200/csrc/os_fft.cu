@@ -43,7 +43,6 @@ struct OsParams {
   i64 npairs;               // segment pairs per signal
   i64 total;                // npairs * batch
   int accumulate;
-  int dbg;
   i64 prefetch_distance;    // work items between a CTA and its successor on the same SM
 };
 
@@ -132,7 +131,6 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     w.cntB = w.haveB ? (int)(remB < p.step ? remB : p.step) : 0;
     w.c_off = p.c_off;
     w.accumulate = p.accumulate != 0;
-    w.dbg = p.dbg;
     fwd_first<P>(t, w, tb, sm);
   }
   if constexpr (P::NPASS == 3) {
@@ -186,7 +184,7 @@ void launch_fused(const OsParams &p, cudaStream_t stream) {
       B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
       wave[dev] = per_sm * sms > 0 ? per_sm * sms : 1;
     }
-    q.prefetch_distance = getenv("B200_NO_PREFETCH") ? 0 : (i64)(dev < 16 ? wave[dev] : 148) * G;
+    q.prefetch_distance = (i64)(dev < 16 ? wave[dev] : 148) * G;
   }
   os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(q);
   b200_prof_end(B200_PROF_FUSED, stream);
@@ -258,7 +256,6 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
   op.x = job.x; op.x_len = job.x_len; op.x_stride = job.x_stride;
   op.out = job.out; op.out_len = job.out_len; op.out_stride = job.out_stride;
   op.tw = tw;
-  op.dbg = getenv("B200_DBG") ? atoi(getenv("B200_DBG")) : 0;
 
 #define B200_DISPATCH(PLAN, GROUPS)                                                    \
   case PLAN::N: {                                                                      \

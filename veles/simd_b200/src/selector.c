@@ -34,7 +34,12 @@ ConvolutionAlgorithm simd_b200_select_algorithm(size_t x_length, size_t h_length
  * impulse responses that would leave less than half a transform of useful output are
  * split into partitions of N/2 taps. */
 int b200_os_pick_n(long long h_len, long long out_len) {
-  if (getenv("B200_FORCE_N")) return atoi(getenv("B200_FORCE_N"));
+  /* tuning knob for selector sweeps (profiles/): VELES_B200_FORCE_N=<power of two> */
+  const char *force = getenv("VELES_B200_FORCE_N");
+  if (force) {
+    int n = atoi(force);
+    if (n >= B200_FFT_MIN && n <= B200_FFT_MAX && (n & (n - 1)) == 0) return n;
+  }
   int best = B200_FFT_MAX;
   double best_cost = 1e300;
   for (int n = B200_FFT_MIN; n <= B200_FFT_MAX; n *= 2) {
