@@ -72,6 +72,44 @@ long long simd_b200_kernel_launches(void);
 void simd_b200_profile(int enable);
 void simd_b200_profile_collect(double *total_ms, long long *count) NOTNULL(1, 2);
 
+/* ---- allocation-free filtering ---------------------------------------------------------
+ * No counterpart in the reference (which allocates with malloc in every *_initialize).
+ *
+ * For callers that must not, or cannot, allocate device memory while they run: code that
+ * lives inside a fixed memory budget handed out by its own arena, plug-ins whose host
+ * forbids cudaMalloc after start-up, and real-time loops where an allocation (an implicit
+ * device synchronisation) would break their deadline.  The handle API cannot serve them:
+ * convolve_overlap_save_initialize() allocates the spectrum scratch and staging buffers.
+ *
+ * result[0 .. x_length+h_length-2] = x (*) h   (reverse = 0, as convolve())
+ *                                  = x (x) h   (reverse != 0, as cross_correlate())
+ * computed by the same fused overlap-save kernels as convolve_overlap_save().  The only
+ * device memory used besides the caller's x, h and result is a pair of arrays built into
+ * the library image (128 KiB of spectrum scratch + 127 KiB of twiddle tables per GPU that
+ * loads the library, held until the process exits).  The call performs no cudaMalloc,
+ * cudaFree or other allocating call, creates no stream or event, and returns after
+ * enqueueing its kernels on `cuda_stream` (a cudaStream_t passed as void*, NULL = the
+ * legacy default stream); it does not wait for them.
+ *
+ * Limits and rules
+ *   - h_length <= 8192 taps (what the 16384-bin scratch array holds); larger values are
+ *     rejected with return code 1 and a message on stderr.  x_length is not limited by it.
+ *   - x, h and result must be device (or managed) memory; host pointers are rejected with
+ *     return code 2, because staging them would take an allocation.  result must not
+ *     overlap x or h.
+ *   - The first call on each device does a one-time set-up with that device current: it
+ *     looks up the device addresses of the built-in arrays, fills the twiddle tables with a
+ *     small kernel on `cuda_stream` and waits for it.  Make that first call before any
+ *     stream capture begins.
+ *   - All calls on one device share the one scratch array, and it keeps whatever the last
+ *     call left in it.  Nothing needs clearing between calls (each call rewrites every bin
+ *     it later reads), but two calls whose kernels can run at the same time on the GPU
+ *     (different streams, or different host threads without ordering) race on it: order
+ *     them on one stream or with events.
+ * Returns 0 on success, 1 size beyond the built-in maximum, 2 bad argument, 3 CUDA error. */
+int simd_b200_filter_noalloc(const float *x, size_t x_length, const float *h,
+                             size_t h_length, int reverse, float *result, void *cuda_stream);
+
 SIMD_API_END
 
 #endif  /* SIMD_B200_EXT_H_ */

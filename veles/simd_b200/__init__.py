@@ -101,6 +101,8 @@ def _load():
     L.simd_b200_profile.restype = None
     L.simd_b200_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
     L.simd_b200_profile_collect.restype = None
+    L.simd_b200_filter_noalloc.argtypes = [vp, sz, vp, sz, C.c_int, vp, vp]
+    L.simd_b200_filter_noalloc.restype = C.c_int
     L.mallocf.argtypes = [sz]
     L.mallocf.restype = vp
     L.malloc_aligned.argtypes = [sz]
@@ -126,7 +128,7 @@ EXPORTED_SYMBOLS = (
     "cross_correlate_batch simd_b200_filter_shard simd_b200_select_algorithm "
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
-    "simd_b200_profile simd_b200_profile_collect").split()
+    "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc").split()
 
 
 def _is_torch(a):

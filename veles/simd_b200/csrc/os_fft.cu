@@ -303,3 +303,124 @@ void b200_os_launch(const OsDevPlan &plan, const DevJob &job, bool single_segmen
   b200_os_launch_with(plan.twiddles, plan.spectrum, plan.n_fft, plan.part_taps, job,
                       single_segment, stream);
 }
+
+// ---- allocation-free entry point ---------------------------------------------------------
+// simd_b200_filter_noalloc (declared in include/simd/b200.h) runs the same two kernels as
+// convolve_overlap_save, but every byte of device memory they need besides the caller's own
+// x, h and result lives in the two file-scope arrays below, which the CUDA runtime places
+// on each GPU when this library is loaded there and keeps until the process exits:
+//   g_noalloc_spectrum   the fused kernel's scratch (the filter spectrum of one call)
+//   g_noalloc_twiddles   read-only twiddle tables for every supported transform length,
+//                        packed back to back (table for length n starts at n/2 - 128)
+// In host code these two names are only handles for the runtime, not device addresses: the
+// address a kernel can use is obtained with cudaGetSymbolAddress, once per device, while
+// that device is current (noalloc_setup below).
+#define B200_NOALLOC_MAX_N 16384          /* complex bins -> 128 KiB of scratch per GPU */
+#define B200_NOALLOC_MAX_TAPS (B200_NOALLOC_MAX_N / 2)
+#define B200_NOALLOC_TW_TOTAL (B200_NOALLOC_MAX_N - 128)   /* sum of n/2 for n = 256..16384 */
+
+static __device__ __align__(256) float2 g_noalloc_spectrum[B200_NOALLOC_MAX_N];
+static __device__ __align__(256) float2 g_noalloc_twiddles[B200_NOALLOC_TW_TOTAL];
+
+namespace {
+
+// Fills every packed twiddle table: entry j of the table for length n is exp(-2*pi*i*j/n),
+// evaluated in double precision on the device (no host buffer, no copy).
+__global__ void noalloc_twiddle_kernel(float2 *tables) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B200_NOALLOC_TW_TOTAL) return;
+  int n = 256;
+  while (i >= n - 128) n *= 2;            // table of length n occupies [n/2 - 128, n - 128)
+  const int j = i - (n / 2 - 128);
+  double s, c;
+  sincospi(-2.0 * (double)j / (double)n, &s, &c);
+  tables[i] = make_float2((float)c, (float)s);
+}
+
+struct NoAllocDevice {
+  bool ready = false;
+  float2 *spectrum = nullptr;
+  float2 *twiddles = nullptr;
+};
+NoAllocDevice g_noalloc_dev[16];
+std::mutex g_noalloc_mu;
+
+// Once per device, with that device current.  Returns cudaSuccess or the failing call's code.
+cudaError_t noalloc_setup(int dev, cudaStream_t stream) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  NoAllocDevice &d = g_noalloc_dev[dev];
+  if (d.ready) return cudaSuccess;
+  cudaError_t err = cudaGetSymbolAddress((void **)&d.spectrum, g_noalloc_spectrum);
+  if (err != cudaSuccess) return err;
+  err = cudaGetSymbolAddress((void **)&d.twiddles, g_noalloc_twiddles);
+  if (err != cudaSuccess) return err;
+  noalloc_twiddle_kernel<<<(B200_NOALLOC_TW_TOTAL + 255) / 256, 256, 0, stream>>>(d.twiddles);
+  err = cudaGetLastError();
+  if (err != cudaSuccess) return err;
+  b200_count_launch(1);
+  d.ready = true;     // later launches on other streams are ordered by the caller (see header)
+  return cudaStreamSynchronize(stream);
+}
+
+bool noalloc_device_accessible(const void *p) {
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+
+// See include/simd/b200.h for the contract.  Returns 0 on success.
+extern "C" __attribute__((visibility("default"))) int simd_b200_filter_noalloc(
+    const float *x, size_t x_length, const float *h, size_t h_length, int reverse,
+    float *result, void *cuda_stream) {
+  if (!x || !h || !result || x_length == 0 || h_length == 0) {
+    fprintf(stderr, "libSimd(b200): simd_b200_filter_noalloc: null pointer or zero length\n");
+    return 2;
+  }
+  if (h_length > B200_NOALLOC_MAX_TAPS) {
+    fprintf(stderr,
+            "libSimd(b200): simd_b200_filter_noalloc: h_length %zu exceeds the %d taps that the "
+            "built-in %d-bin scratch array can hold; use convolve_overlap_save for longer "
+            "impulse responses\n",
+            h_length, B200_NOALLOC_MAX_TAPS, B200_NOALLOC_MAX_N);
+    return 1;
+  }
+  if (x_length + h_length - 1 >= ((size_t)1 << 40)) {
+    fprintf(stderr, "libSimd(b200): simd_b200_filter_noalloc: signal too long\n");
+    return 1;
+  }
+  if (!noalloc_device_accessible(x) || !noalloc_device_accessible(h) ||
+      !noalloc_device_accessible(result)) {
+    fprintf(stderr,
+            "libSimd(b200): simd_b200_filter_noalloc: x, h and result must be device memory "
+            "(staging host buffers would need an allocation)\n");
+    return 2;
+  }
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess || dev < 0 || dev >= 16) {
+    fprintf(stderr, "libSimd(b200): simd_b200_filter_noalloc: no usable CUDA device\n");
+    return 3;
+  }
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  err = noalloc_setup(dev, stream);
+  if (err != cudaSuccess) {
+    fprintf(stderr, "libSimd(b200): simd_b200_filter_noalloc: set-up failed: %s\n",
+            cudaGetErrorString(err));
+    return 3;
+  }
+  // transform length: the library's usual choice, raised until all taps fit one spectrum
+  int n = b200_os_pick_n((long long)h_length, (long long)(x_length + h_length - 1));
+  while ((size_t)(n / 2) < h_length) n *= 2;
+  DevJob job;
+  job.x = x; job.x_len = (i64)x_length; job.x_stride = (i64)x_length;
+  job.h = h; job.h_len = (i64)h_length;
+  job.out = result; job.out_len = (i64)(x_length + h_length - 1); job.out_stride = job.out_len;
+  job.pad = (i64)h_length - 1; job.batch = 1; job.reverse = reverse ? 1 : 0;
+  const NoAllocDevice &d = g_noalloc_dev[dev];
+  // every bin of the spectrum array is rewritten by the spectrum kernel of this call, so
+  // nothing left over from the previous call is ever read
+  b200_os_launch_with(d.twiddles + (n / 2 - 128), d.spectrum, n, (int)h_length, job, false, stream);
+  return 0;
+}
