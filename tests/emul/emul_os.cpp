@@ -20,7 +20,7 @@ static void make_twiddles(std::vector<float2> &tw) {
   }
 }
 
-template <class P, int NB, int R>
+template <class P, int NB, int R, int MODE>
 static int conflicts_of_pass() {
   using G = PassGeom<P, NB, R>;
   int worst = 1;
@@ -30,7 +30,9 @@ static int conflicts_of_pass() {
         int cnt[16] = {0};
         for (int t = t0; t < t0 + 16 && t < P::T; t++) {
           int base, npp, bf;
-          G::locate(t, j, base, npp, bf);
+          if (MODE == 1) G::locate_mid(t, j, base, npp, bf);
+          else if (MODE == 2 && P::NPASS == 3) G::locate_centre(t, j, base, npp, bf);
+          else G::locate(t, j, base, npp, bf);
           cnt[pad_pos(base + r * G::S) % 16]++;
         }
         for (int b = 0; b < 16; b++) if (cnt[b] > worst) worst = cnt[b];
@@ -76,13 +78,26 @@ static int run_plan(const char *name, int h_len, int x_len, int reverse) {
     w.c_off = h_len - 1;
     w.accumulate = false;
     for (int t = 0; t < P::T; t++) fwd_first<P>(t, w, tb[t], sm.data());
-    if (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
-    for (int t = 0; t < P::T; t++) {
-      HRegs<P> hr;
-      load_spectrum<P>(t, Hperm.data(), hr);
-      centre<P>(t, hr, sm.data());
+    if constexpr (P::NPASS == 3) {
+      // the three middle phases need only warp-level ordering: run them warp by warp, each
+      // warp all the way through before the next one starts (and in reverse warp order)
+      for (int w0 = (P::T - 1) / 32 * 32; w0 >= 0; w0 -= 32) {
+        const int w1 = w0 + 32 < P::T ? w0 + 32 : P::T;
+        for (int t = w0; t < w1; t++) fwd_mid<P>(t, tb[t], sm.data());
+        for (int t = w0; t < w1; t++) {
+          HRegs<P> hr;
+          load_spectrum<P>(t, Hperm.data(), hr);
+          centre<P>(t, hr, sm.data());
+        }
+        for (int t = w0; t < w1; t++) inv_mid<P>(t, tb[t], sm.data());
+      }
+    } else {
+      for (int t = 0; t < P::T; t++) {
+        HRegs<P> hr;
+        load_spectrum<P>(t, Hperm.data(), hr);
+        centre<P>(t, hr, sm.data());
+      }
     }
-    if (P::NPASS == 3) for (int t = 0; t < P::T; t++) inv_mid<P>(t, tb[t], sm.data());
     for (int t = 0; t < P::T; t++) inv_last<P>(t, w, tb[t], sm.data());
   }
   // double-precision check
@@ -99,9 +114,10 @@ static int run_plan(const char *name, int h_len, int x_len, int reverse) {
     if (fabs(d) > maxabs) maxabs = fabs(d);
   }
   double rel = sqrt(num / den);
-  int c1 = conflicts_of_pass<P, P::N, P::R1>();
-  int c2 = P::NPASS == 3 ? conflicts_of_pass<P, P::NB2, P::R2>() : 1;
-  int c3 = conflicts_of_pass<P, P::R3, P::R3>();
+  int c1 = conflicts_of_pass<P, P::N, P::R1, 0>();
+  int c2 = 1;
+  if constexpr (P::NPASS == 3) c2 = conflicts_of_pass<P, P::NB2, P::R2, 1>();
+  int c3 = conflicts_of_pass<P, P::R3, P::R3, 2>();
   printf("%-22s N=%5d h=%5d x=%6d rev=%d nseg=%3d rel_l2=%.3e maxabs=%.3e conflicts=%d/%d/%d\n",
          name, P::N, h_len, x_len, reverse, nseg, rel, maxabs, c1, c2, c3);
   return (rel < 2e-6 && c1 == 1 && c2 == 1 && c3 == 1) ? 0 : 1;

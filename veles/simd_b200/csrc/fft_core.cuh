@@ -169,6 +169,8 @@ struct Plan {
   static_assert(R1 * R2 * R3 == N, "radices must multiply to N");
   static_assert(E % R1 == 0 && E % R2 == 0 && E % R3 == 0, "E must be a multiple of each radix");
   static_assert(NPASS == 3 || R3 == NB2, "two-pass plan: R3 = N/R1");
+  static_assert(NPASS == 2 || (R3 == 16 && R2 % 16 == 0 && T % 16 == 0 && (N / R1) == R2 * 16),
+                "three-pass plans: 16-point centre, half-warp-closed middle passes");
 };
 
 // Where butterfly number j of thread t lives for a pass with block length NB and radix R.
@@ -181,6 +183,28 @@ struct PassGeom {
     int blk = bf / S;
     npp = bf % S;
     base = blk * NB + npp;
+  }
+  // Middle-pass geometry of 3-pass plans, arranged so that everything a half-warp touches
+  // between the first and the last pass stays inside that half-warp: after the first pass
+  // the R1 sub-blocks of NB2 = R2*16 points are independent transforms, and half-warp g
+  // (threads 16g..16g+15) owns sub-blocks g*HB .. g*HB+HB-1 (HB = E/R2) through the second
+  // forward pass, the centre and the first inverse pass.  Only warp-level synchronisation
+  // is needed between those three phases, so warps drift apart and one warp's shared-memory
+  // traffic overlaps another's arithmetic.
+  FC_HD static void locate_mid(int t, int j, int &base, int &npp, int &bf) {
+    // pass over sub-blocks of NB = NB2 with radix R = R2, S = 16: butterfly j of thread t
+    const int blk = (t >> 4) * (P::E / P::R2) + j;
+    npp = t & 15;
+    bf = blk * S + npp;
+    base = blk * NB + npp;
+  }
+  FC_HD static void locate_centre(int t, int j, int &base, int &npp, int &bf) {
+    // contiguous 16-point butterflies: sub-block has R2 of them, R2/16 per thread
+    constexpr int PER = P::R2 / 16;
+    const int blk = (t >> 4) * (P::E / P::R2) + j / PER;
+    bf = blk * P::R2 + (t & 15) + 16 * (j % PER);
+    npp = 0;
+    base = bf * NB;
   }
   // Padded shared-memory offset of element r relative to pad_pos(base): a compile-time
   // constant, because r*S is a multiple of 16 (S % 16 == 0) or stays inside base's 16-slot
@@ -226,7 +250,7 @@ FC_HD void load_twiddle_bases(int t, const float2 *tw, TwBases<P> &tb) {
     static_for<0, P::E / P::R2>([&](auto jj) {
       constexpr int j = decltype(jj)::value;
       int base, npp, bf;
-      PassGeom<P, P::NB2, P::R2>::locate(t, j, base, npp, bf);
+      PassGeom<P, P::NB2, P::R2>::locate_mid(t, j, base, npp, bf);
       tb.w2[j] = tw[npp * P::R1];
     });
   }
@@ -315,7 +339,7 @@ FC_HD void fwd_mid(int t, const TwBases<P> &tb, float2 *sm) {
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
-    G::locate(t, j, base, npp, bf);
+    G::locate_mid(t, j, base, npp, bf);
     auto *smb = sm + pad_pos(base);
     float2 v[R];
     static_for<0, R>([&](auto rr) {
@@ -346,7 +370,7 @@ FC_HD void centre(int t, const HRegs<P> &hr, float2 *sm) {
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
-    G::locate(t, j, base, npp, bf);
+    if constexpr (P::NPASS == 3) G::locate_centre(t, j, base, npp, bf); else G::locate(t, j, base, npp, bf);
     auto *smb = sm + pad_pos(base);
     float2 v[R], u[R];
     static_for<0, R>([&](auto rr) {
@@ -374,7 +398,7 @@ FC_HD void centre_store_spectrum(int t, float2 *Hperm, float scale, const float2
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
-    G::locate(t, j, base, npp, bf);
+    if constexpr (P::NPASS == 3) G::locate_centre(t, j, base, npp, bf); else G::locate(t, j, base, npp, bf);
     auto *smb = sm + pad_pos(base);
     float2 v[R];
     static_for<0, R>([&](auto rr) {
@@ -397,7 +421,7 @@ FC_HD void inv_mid(int t, const TwBases<P> &tb, float2 *sm) {
   static_for<0, P::E / R>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
     int base, npp, bf;
-    G::locate(t, j, base, npp, bf);
+    G::locate_mid(t, j, base, npp, bf);
     auto *smb = sm + pad_pos(base);
     float2 v[R];
     Powers<R> pw;

@@ -133,19 +133,22 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     w.accumulate = p.accumulate != 0;
     fwd_first<P>(t, w, tb, sm);
   }
+  __syncthreads();
   if constexpr (P::NPASS == 3) {
-    __syncthreads();
+    // Between the first and the last pass every half-warp works on sub-blocks nobody else
+    // touches (PassGeom::locate_mid / locate_centre), so warp-level barriers suffice and the
+    // warps of a CTA run these three phases out of step with each other.
     if (live) fwd_mid<P>(t, tb, sm);
-  }
-  // the filter spectrum does not depend on shared memory: fetch it across the barrier
-  if (live) load_spectrum<P>(t, p.spectrum, hr);
-  __syncthreads();
-  if (live) centre<P>(t, hr, sm);
-  __syncthreads();
-  if constexpr (P::NPASS == 3) {
+    if (live) load_spectrum<P>(t, p.spectrum, hr);
+    __syncwarp();
+    if (live) centre<P>(t, hr, sm);
+    __syncwarp();
     if (live) inv_mid<P>(t, tb, sm);
-    __syncthreads();
+  } else {
+    if (live) load_spectrum<P>(t, p.spectrum, hr);
+    if (live) centre<P>(t, hr, sm);
   }
+  __syncthreads();
   if (live) inv_last<P>(t, w, tb, sm);
 }
 
