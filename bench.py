@@ -294,7 +294,11 @@ def main():
     value = outputs_per_step / (ms_per_step * 1e-3) / 1e9
 
     # ---- roofline of the dominant kernel (per launch, from its own events) ----------------
-    kind = "direct" if alg == 0 else "fused"
+    # the batched call may cross over from the handle's single-signal choice (selector.c)
+    kind = "fused" if prof["fused"][1] > 0 else "direct"
+    if kind == "fused" and alg == 0:
+        alg = 2
+        n_fft = v.transform_length(x_len, h_len)
     k_ms, k_cnt = prof[kind]
     k_avg_ms = k_ms / max(k_cnt, 1)
     launches_per_step = max(k_cnt // args.steps, 1)

@@ -47,6 +47,10 @@ void simd_b200_filter_shard(const float *x, size_t x_length, const float *h,
  * The decision convolve_initialize makes on B200 (replaces the 2h / 200 / 350 rules of
  * reference src/convolve.c:349-363) and the transform length the FFT-based paths use. */
 ConvolutionAlgorithm simd_b200_select_algorithm(size_t x_length, size_t h_length);
+/* Same decision for `batch` signals sharing one h (what convolve_batch re-evaluates when its
+ * handle says brute force: many short-filter signals are faster through the transform path). */
+ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_length,
+                                                      size_t batch);
 int simd_b200_transform_length(size_t x_length, size_t h_length);
 
 /* ---- stream and device control --------------------------------------------------------

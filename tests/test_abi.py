@@ -29,7 +29,7 @@ def _declared_functions():
 
 def test_library_exports_every_declared_symbol(simd):
     declared = _declared_functions()
-    assert len(declared) >= 34
+    assert len(declared) >= 36
     out = subprocess.run(["nm", "-D", "--defined-only", simd.LIB_PATH], capture_output=True,
                          text=True, check=True).stdout
     exported = {l.split()[-1] for l in out.splitlines() if " T " in l}
@@ -93,10 +93,15 @@ def test_headers_compile_as_cxx(tmp_path):
 
 
 def test_selector_is_pure_host_logic(simd):
-    # BASELINE configs: C1 small -> direct; C3 h=64 -> direct; C2/C4/C5 -> overlap-save
+    # BASELINE configs on the measured B200 cost model (profiles/selector_sweep_r01.md):
+    # single small signals are launch-bound -> one direct launch; C4/C5 -> overlap-save;
+    # the C3 *batch* (4096 signals, h=64) crosses over to the transform path
     assert simd.select_algorithm(1024, 50) == simd.ALG_BRUTE_FORCE
     assert simd.select_algorithm(16384, 64) == simd.ALG_BRUTE_FORCE
-    assert simd.select_algorithm(65536, 512) == simd.ALG_OVERLAP_SAVE
+    assert simd.select_algorithm(16384, 64, batch=4096) == simd.ALG_OVERLAP_SAVE
+    assert simd.select_algorithm(16384, 8, batch=4096) == simd.ALG_BRUTE_FORCE
+    assert simd.select_algorithm(65536, 512) == simd.ALG_BRUTE_FORCE
+    assert simd.select_algorithm(1 << 20, 512) == simd.ALG_OVERLAP_SAVE
     assert simd.select_algorithm(262144, 4096) == simd.ALG_OVERLAP_SAVE
     assert simd.select_algorithm(2 ** 30, 8192) == simd.ALG_OVERLAP_SAVE
     assert simd.select_algorithm(100000, 90000) == simd.ALG_FFT        # x <= 2h, large
@@ -105,6 +110,7 @@ def test_selector_is_pure_host_logic(simd):
         assert 256 <= n <= 16384 and n & (n - 1) == 0
     assert simd.transform_length(5000, 3000) == 8192      # whole signal: next pow2 >= x+h-1
     assert simd.transform_length(262144, 4096) == 16384
+    assert simd.transform_length(1 << 20, 64) == 2048
 
 
 def test_memory_helpers(simd):

@@ -122,7 +122,8 @@ def test_fft_shapes_and_handle_reuse(simd, oracle, xl, hl):
 
 
 def test_best_method_handle_matches_every_algorithm(simd, oracle):
-    for xl, hl in [(1024, 50), (65536, 512), (16384, 64), (6000, 5000), (40000, 300)]:
+    for xl, hl in [(1024, 50), (65536, 512), (16384, 64), (6000, 5000), (40000, 300),
+                   (1 << 20, 700)]:
         x, h = uni(xl, xl), uni(hl, hl)
         want = oracle.convolve_f64(x, h)
         with simd.Handle(xl, hl) as hd:
@@ -194,7 +195,8 @@ def test_batch_c3_shape(simd, oracle):
     with simd.Handle(xl, hl, "", True) as hd:
         yc = hd(x[:64].contiguous(), torch.flip(h, [0]).contiguous())
         torch.cuda.synchronize()
-    assert torch.equal(yc, y[:64])
+    # (64 signals stay on the direct kernel, 4096 cross over to the transform path)
+    assert rel_l2(yc.cpu().numpy(), y[:64].cpu().numpy()) < 2e-6
 
 
 def test_batch_c4_shape(simd, oracle, reference_or_none):

@@ -89,6 +89,8 @@ def _load():
     L.simd_b200_filter_shard.restype = None
     L.simd_b200_select_algorithm.argtypes = [sz, sz]
     L.simd_b200_select_algorithm.restype = C.c_int
+    L.simd_b200_select_algorithm_batch.argtypes = [sz, sz, sz]
+    L.simd_b200_select_algorithm_batch.restype = C.c_int
     L.simd_b200_transform_length.argtypes = [sz, sz]
     L.simd_b200_transform_length.restype = C.c_int
     L.simd_b200_set_stream.argtypes = [vp]
@@ -126,6 +128,7 @@ EXPORTED_SYMBOLS = (
     "cross_correlate_overlap_save_finalize cross_correlate_initialize cross_correlate "
     "cross_correlate_finalize mallocf malloc_aligned memsetf rmemcpyf convolve_batch "
     "cross_correlate_batch simd_b200_filter_shard simd_b200_select_algorithm "
+    "simd_b200_select_algorithm_batch "
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
     "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc").split()
@@ -170,8 +173,8 @@ def profile_collect():
     return {k: (ms[i], cnt[i]) for i, k in enumerate(("direct", "fused", "spectrum"))}
 
 
-def select_algorithm(x_length, h_length):
-    return lib.simd_b200_select_algorithm(x_length, h_length)
+def select_algorithm(x_length, h_length, batch=1):
+    return lib.simd_b200_select_algorithm_batch(x_length, h_length, batch)
 
 
 def transform_length(x_length, h_length):

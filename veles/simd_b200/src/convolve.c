@@ -205,8 +205,16 @@ static void batch_dispatch(ConvolutionHandle handle, const float *x, size_t x_st
                result, result_stride, batch, handle.handle.os.reverse);
       break;
     case kConvolutionAlgorithmBruteForce:
-      run_full(NULL, B200_ALG_DIRECT, x, xl, x_stride, h, hl, result, result_stride, batch,
-               brute_reverse);
+      /* The handle was chosen for one signal.  A large batch can cross over to the fused
+       * transform kernels (profiles/selector_sweep_r01.md); those then run without a handle,
+       * on the per-device context's scratch. */
+      if (simd_b200_select_algorithm_batch(xl, hl, batch) == kConvolutionAlgorithmBruteForce) {
+        run_full(NULL, B200_ALG_DIRECT, x, xl, x_stride, h, hl, result, result_stride, batch,
+                 brute_reverse);
+      } else {
+        run_full(NULL, B200_ALG_OS, x, xl, x_stride, h, hl, result, result_stride, batch,
+                 brute_reverse);
+      }
       break;
   }
 }

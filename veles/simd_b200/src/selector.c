@@ -14,25 +14,36 @@
 #include <stdlib.h>
 #include "../csrc/b200_internal.h"
 
-/* Direct kernel wins while the impulse response is short (FP32-bound at 2*h FLOP/output,
- * the fused FFT path costs ~50-100 FLOP/output plus a second launch for the spectrum) or
- * while the whole problem is too small to amortise two launches. */
-#define B200_DIRECT_MAX_TAPS 64
-#define B200_DIRECT_MAX_WORK (1LL << 21)     /* x*h multiply-adds */
+/* Cost model fitted to B200 timings (profiles/selector_sweep_r01.md, device-resident data).
+ *
+ *   direct kernel        t = 9 us + 4.5e-8 us per multiply-add        (one launch)
+ *   fused overlap-save   t = 15 us + c(N) * outputs/67.1e6 * N/(N-taps+1) per partition
+ *                        (two launches; c(N) = us per 67.1e6 outputs at 100 % segment use)
+ *
+ * c(N) is not monotone in N: transforms up to 2048 points run many CTAs per SM and overlap
+ * shared-memory traffic with arithmetic, the 8192/16384-point plans run 2 / 1 CTA per SM. */
+static const struct { int n; double c; } kFusedCost[] = {
+  {256, 118.0}, {512, 147.0}, {1024, 145.0}, {2048, 147.0}, {4096, 196.0}, {8192, 210.0},
+  {16384, 255.0},
+};
+#define B200_DIRECT_US_PER_MAC 4.5e-8
+#define B200_DIRECT_LAUNCH_US 9.0
+#define B200_FUSED_LAUNCH_US 15.0
 
-ConvolutionAlgorithm simd_b200_select_algorithm(size_t x_length, size_t h_length) {
-  long long work = (long long)x_length * (long long)h_length;
-  if (h_length <= B200_DIRECT_MAX_TAPS || work <= B200_DIRECT_MAX_WORK) {
-    return kConvolutionAlgorithmBruteForce;
-  }
-  if (x_length > h_length * 2) return kConvolutionAlgorithmOverlapSave;
-  return kConvolutionAlgorithmFFT;
+static double fused_cost_us(int n, double c, long long h_len, long long out_len,
+                            long long batch) {
+  long long taps = h_len < n / 2 ? h_len : n / 2;
+  long long parts = (h_len + taps - 1) / taps;
+  double step = (double)(n - taps + 1);
+  /* whole segment pairs are executed, so short outputs pay for a full pair */
+  double nseg = (double)((out_len + (long long)step - 1) / (long long)step);
+  double pairs = (double)(((long long)nseg + 1) / 2);
+  double points = pairs * 2.0 * n * (double)batch;       /* real samples transformed */
+  return B200_FUSED_LAUNCH_US + (double)parts * c * points / 67.1e6;
 }
 
 /* Transform length for an impulse response of h_len taps producing out_len outputs per
- * signal.  Cost model: transforms executed (segment pairs x partitions) x N*(log2 N + 2);
- * impulse responses that would leave less than half a transform of useful output are
- * split into partitions of N/2 taps. */
+ * signal; impulse responses longer than N/2 taps are split into partitions of N/2 taps. */
 int b200_os_pick_n(long long h_len, long long out_len) {
   /* tuning knob for selector sweeps (profiles/): VELES_B200_FORCE_N=<power of two> */
   const char *force = getenv("VELES_B200_FORCE_N");
@@ -42,18 +53,31 @@ int b200_os_pick_n(long long h_len, long long out_len) {
   }
   int best = B200_FFT_MAX;
   double best_cost = 1e300;
-  for (int n = B200_FFT_MIN; n <= B200_FFT_MAX; n *= 2) {
-    long long taps = h_len < n / 2 ? h_len : n / 2;
-    long long parts = (h_len + taps - 1) / taps;
-    long long step = n - taps + 1;
-    long long nseg = (out_len + step - 1) / step;
-    long long pairs = (nseg + 1) / 2;
-    int lg = 0;
-    while ((1 << lg) < n) lg++;
-    double cost = (double)parts * (double)pairs * (double)n * (lg + 2.0);
-    if (cost < best_cost * 0.999) { best_cost = cost; best = n; }
+  for (unsigned i = 0; i < sizeof(kFusedCost) / sizeof(kFusedCost[0]); i++) {
+    double cost = fused_cost_us(kFusedCost[i].n, kFusedCost[i].c, h_len, out_len, 1);
+    if (cost < best_cost * 0.999) { best_cost = cost; best = kFusedCost[i].n; }
   }
   return best;
+}
+
+/* Handle-time decision for `batch` signals (the reference API has no batch: batch = 1). */
+ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_length,
+                                                      size_t batch) {
+  long long out_len = (long long)x_length + (long long)h_length - 1;
+  double direct = B200_DIRECT_LAUNCH_US +
+                  B200_DIRECT_US_PER_MAC * (double)batch * (double)x_length * (double)h_length;
+  int n = b200_os_pick_n((long long)h_length, out_len);
+  double c = 255.0;
+  for (unsigned i = 0; i < sizeof(kFusedCost) / sizeof(kFusedCost[0]); i++)
+    if (kFusedCost[i].n == n) c = kFusedCost[i].c;
+  double fused = fused_cost_us(n, c, (long long)h_length, out_len, (long long)batch);
+  if (direct <= fused) return kConvolutionAlgorithmBruteForce;
+  if (x_length > h_length * 2) return kConvolutionAlgorithmOverlapSave;
+  return kConvolutionAlgorithmFFT;
+}
+
+ConvolutionAlgorithm simd_b200_select_algorithm(size_t x_length, size_t h_length) {
+  return simd_b200_select_algorithm_batch(x_length, h_length, 1);
 }
 
 int b200_os_part_taps(int n_fft, long long h_len) {
