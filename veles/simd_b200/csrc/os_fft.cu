@@ -62,6 +62,9 @@ __global__ void __launch_bounds__(P::T) os_spectrum_kernel(SpecParams p) {
   float2 *sm = reinterpret_cast<float2 *>(smem4);
   const int t = threadIdx.x;
   const int part = blockIdx.x;
+  // programmatic dependent launch: the fused kernel behind us may start now; it only needs
+  // the spectrum at its centre pass and waits there (griddepcontrol.wait)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // correlation-form taps of this partition: g[j], j in [j0, j0+taps); its convolution-form
   // impulse response is gf[m] = g[j0+taps-1-m]  (g[j] = reverse ? h[j] : h[h_len-1-j]).
   const i64 j0 = (i64)part * p.part_taps;
@@ -139,12 +142,16 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     // touches (PassGeom::locate_mid / locate_centre), so warp-level barriers suffice and the
     // warps of a CTA run these three phases out of step with each other.
     if (live) fwd_mid<P>(t, tb, sm);
+    // the spectrum kernel may still be running (programmatic dependent launch): everything
+    // above overlapped with it, the spectrum itself is needed from here on
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (live) load_spectrum<P>(t, p.spectrum, hr);
     __syncwarp();
     if (live) centre<P>(t, hr, sm);
     __syncwarp();
     if (live) inv_mid<P>(t, tb, sm);
   } else {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (live) load_spectrum<P>(t, p.spectrum, hr);
     if (live) centre<P>(t, hr, sm);
   }
@@ -163,7 +170,7 @@ using P8192 = Plan<8192, 32, 32, 16, 16>;   // 256               1
 using P16384 = Plan<16384, 32, 32, 32, 16>; // 512               1
 
 template <class P, int G>
-void launch_fused(const OsParams &p, cudaStream_t stream) {
+void launch_fused(const OsParams &p, cudaStream_t stream, bool after_spectrum) {
   static bool configured[16] = {false};
   size_t smem = sizeof(float2) * P::SMEM_FLOAT2 * G;
   int dev = 0;
@@ -189,7 +196,22 @@ void launch_fused(const OsParams &p, cudaStream_t stream) {
     }
     q.prefetch_distance = (i64)(dev < 16 ? wave[dev] : 148) * G;
   }
-  os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(q);
+  if (after_spectrum) {
+    // launched right behind the spectrum kernel: let it start before that kernel finishes
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(P::T * G);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, os_fused_kernel<P, G>, q));
+  } else {
+    os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(q);
+  }
   b200_prof_end(B200_PROF_FUSED, stream);
   B200_CUDA_CHECK(cudaGetLastError());
   b200_count_launch(1);
@@ -281,7 +303,7 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
       op.nseg = (job.out_len + op.step - 1) / op.step;                                 \
       op.npairs = (op.nseg + 1) / 2;                                                   \
       op.total = op.npairs * job.batch;                                                \
-      launch_fused<PLAN, GROUPS>(op, stream);                                          \
+      launch_fused<PLAN, GROUPS>(op, stream, q == 0);                                  \
     }                                                                                  \
   } break;
 
