@@ -123,6 +123,69 @@ static int run_plan(const char *name, int h_len, int x_len, int reverse) {
   return (rel < 2e-6 && c1 == 1 && c2 == 1 && c3 == 1) ? 0 : 1;
 }
 
+// Real-packed mode: one real segment of 2N samples per transform.
+template <class P>
+static int run_plan_real(const char *name, int h_len, int x_len, int reverse, int pad_extra) {
+  std::vector<float2> tw;
+  make_twiddles<P>(tw);
+  std::vector<float> x(x_len), h(h_len);
+  unsigned s = 777u + h_len;
+  auto rnd = [&]() { s = s * 1664525u + 1013904223u; return ((s >> 8) & 0xFFFF) / 32768.0f - 1.0f; };
+  for (auto &v : x) v = rnd();
+  for (auto &v : h) v = rnd();
+  std::vector<TwBases<P>> tb(P::T);
+  for (int t = 0; t < P::T; t++) load_twiddle_bases<P>(t, tw.data(), tb[t]);
+  std::vector<float2> sm(P::SMEM_FLOAT2);
+  std::vector<float4> AB(P::N);
+  i64 start = reverse ? h_len - 1 : 0;
+  int dir = reverse ? -1 : 1;
+  for (int t = 0; t < P::T; t++) spec_first_real<P>(t, h.data(), start, dir, h_len, tb[t], sm.data());
+  if constexpr (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
+  for (int t = 0; t < P::T; t++) centre_real_fwd<P>(t, sm.data());
+  for (int t = 0; t < P::T; t++) centre_real_coeffs<P>(t, AB.data(), 1.0f / P::N, sm.data());
+
+  const int L = 2 * P::N;
+  const int out_len = x_len + h_len - 1;
+  const int pad = h_len - 1;
+  const int e = pad_extra;                 // extra leading samples (alignment shift)
+  const int c_off = h_len - 1 + e;
+  const int step = (L - c_off) & ~1;
+  const int nseg = (out_len + step - 1) / step;
+  std::vector<float> out(out_len, NAN);
+  std::vector<float2> u((size_t)P::T * P::E);
+  for (int sg = 0; sg < nseg; sg++) {
+    SegReal w;
+    w.x = x.data(); w.x_len = x_len;
+    w.in0 = (i64)sg * step - pad - e;
+    w.out = out.data(); w.out0 = (i64)sg * step;
+    i64 rem = out_len - w.out0;
+    w.cnt = (int)(rem < step ? rem : step);
+    w.c_off = c_off; w.accumulate = false;
+    for (int t = 0; t < P::T; t++) fwd_first_real<P>(t, w, tb[t], sm.data());
+    if constexpr (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
+    for (int t = 0; t < P::T; t++) centre_real_fwd<P>(t, sm.data());
+    for (int t = 0; t < P::T; t++) centre_real_mix<P>(t, AB.data(), sm.data(), u.data() + (size_t)t * P::E);
+    for (int t = 0; t < P::T; t++) centre_real_store<P>(t, sm.data(), u.data() + (size_t)t * P::E);
+    if constexpr (P::NPASS == 3) for (int t = 0; t < P::T; t++) inv_mid<P>(t, tb[t], sm.data());
+    for (int t = 0; t < P::T; t++) inv_last_real<P>(t, w, tb[t], sm.data());
+  }
+  double num = 0, den = 0;
+  for (int n = 0; n < out_len; n++) {
+    double acc = 0;
+    for (int m = 0; m < h_len; m++) {
+      int i = n - m;
+      if (i >= 0 && i < x_len) acc += (double)(reverse ? h[h_len - 1 - m] : h[m]) * x[i];
+    }
+    if (!(out[n] == out[n])) { printf("%s real: NaN/unwritten at %d\n", name, n); return 1; }
+    double d = out[n] - acc;
+    num += d * d; den += acc * acc;
+  }
+  double rel = sqrt(num / den);
+  printf("%-22s real-packed N=%5d h=%5d x=%6d rev=%d e=%d nseg=%3d rel_l2=%.3e\n", name, P::N, h_len,
+         x_len, reverse, e, nseg, rel);
+  return rel < 2e-6 ? 0 : 1;
+}
+
 int main() {
   int bad = 0;
   bad += run_plan<Plan<256, 16, 16, 1, 16>>("256=16x16", 50, 1024, 0);
@@ -134,6 +197,11 @@ int main() {
   bad += run_plan<Plan<8192, 32, 32, 16, 16>>("8192=32x16x16", 2048, 30000, 0);
   bad += run_plan<Plan<16384, 32, 32, 32, 16>>("16384=32x32x16", 4096, 60000, 0);
   bad += run_plan<Plan<16384, 32, 32, 32, 16>>("16384=32x32x16", 8192, 40000, 1);
+  bad += run_plan_real<Plan<256, 16, 16, 1, 16>>("256=16x16", 100, 3000, 0, 1);
+  bad += run_plan_real<Plan<512, 16, 2, 16, 16>>("512=2x16x16", 300, 4000, 1, 0);
+  bad += run_plan_real<Plan<2048, 16, 8, 16, 16>>("2048=8x16x16", 1500, 20000, 0, 0);
+  bad += run_plan_real<Plan<8192, 32, 32, 16, 16>>("8192=32x16x16", 6000, 50000, 1, 1);
+  bad += run_plan_real<Plan<16384, 32, 32, 32, 16>>("16384=32x32x16", 8192, 100000, 0, 1);
   printf(bad ? "EMUL FAIL (%d)\n" : "EMUL OK\n", bad);
   return bad ? 1 : 0;
 }

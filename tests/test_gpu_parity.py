@@ -310,6 +310,50 @@ def test_host_pointer_pipeline_batches_and_long_signals(simd, oracle):
             assert ok, (xl, hl, n0, r, m)
 
 
+def test_real_packed_mode(simd, oracle, monkeypatch):
+    """The real-packed transform mode (one real segment of 2N samples per transform, used
+    when the impulse response is long relative to N) forced on for shapes the cost model
+    would not necessarily send there, against the oracle and against the paired mode."""
+    import torch
+    simd.use_torch_stream()
+    for xl, hl, n in [(3000, 100, 256), (4001, 301, 512), (20000, 1000, 1024), (20001, 1500, 2048),
+                      (60000, 3000, 4096), (50000, 6000, 8192), (70000, 8192, 16384),
+                      (100000, 12000, 16384), (40001, 16384, 16384)]:
+        x, h = uni(xl + 11, xl), uni(hl + 12, hl)
+        for corr in (False, True):
+            want = oracle.convolve_fft(x, h, corr)
+            monkeypatch.setenv("VELES_B200_REAL", "1")
+            monkeypatch.setenv("VELES_B200_FORCE_N", str(n))
+            with simd.Handle(xl, hl, "_overlap_save", corr) as hd:
+                assert hd.transform_length == n
+                got = hd(x, h)
+                got2 = hd(x, h)                      # handle reuse
+            monkeypatch.delenv("VELES_B200_REAL")
+            monkeypatch.delenv("VELES_B200_FORCE_N")
+            check(got, want, x, h, f"real-packed {xl}x{hl} N={n} corr={corr}")
+            assert np.array_equal(got, got2)
+    # batch + device pointers + shard primitive (pad = 0, odd/even result lengths)
+    xl, hl = 90000, 8000
+    xb, h = uni(3, 5, xl), uni(4, hl)
+    monkeypatch.setenv("VELES_B200_REAL", "1")
+    with simd.Handle(xl, hl, "_overlap_save") as hd:
+        inner = simd.ConvolutionHandle()
+        inner.algorithm, inner.x_length, inner.h_length = 2, xl, hl
+        inner.handle.os = hd.handle
+        xd, hd_ = torch.from_numpy(xb).cuda(), torch.from_numpy(h).cuda()
+        yd = torch.empty((5, xl + hl - 1), device="cuda")
+        simd.lib.convolve_batch(inner, xd.data_ptr(), xl, hd_.data_ptr(), yd.data_ptr(), xl + hl - 1, 5)
+        torch.cuda.synchronize()
+    for b in (0, 4):
+        check(yd[b].cpu().numpy(), oracle.convolve_fft(xb[b], h, 0), xb[b], h, f"real-packed batch row {b}")
+    x = xb[0]
+    full = oracle.convolve_fft(x, h, 0)
+    cut = 45001
+    second = simd.filter_shard(x[cut - (hl - 1):], h, 0, 0, xl + hl - 1 - cut, algorithm=2)
+    check(second, full[cut:], x, h, "real-packed shard")
+    monkeypatch.delenv("VELES_B200_REAL")
+
+
 def test_kernel_launch_counter(simd):
     before = simd.lib.simd_b200_kernel_launches()
     simd.convolve_simd(KAT_X, KAT_H)

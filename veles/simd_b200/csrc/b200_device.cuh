@@ -50,6 +50,7 @@ struct OsDevPlan {
   int n_fft;            // complex transform length
   int part_taps;        // impulse-response taps handled per partition
   int max_parts;        // capacity of `spectrum` in partitions
+  bool real_packed;     // one real segment of 2*n_fft samples per transform (single partition)
   float2 *spectrum;     // [max_parts][n_fft] filter spectra in register order (scratch)
   const float2 *twiddles;  // W_n^j, j < n_fft/2
 };
@@ -59,6 +60,9 @@ void b200_os_launch(const OsDevPlan &plan, const DevJob &job, bool single_segmen
 // Same, with caller-supplied spectrum scratch and twiddles (no allocation on this path).
 void b200_os_launch_with(const float2 *twiddles, float2 *spectrum, int n_fft, int part_taps,
                          const DevJob &job, bool single_segment, cudaStream_t stream);
+
+void b200_os_launch_real(const float2 *twiddles, float4 *coeffs, int n_fft, const DevJob &job,
+                         cudaStream_t stream);
 
 void b200_count_launch(int n);
 

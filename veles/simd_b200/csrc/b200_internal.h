@@ -40,7 +40,8 @@ typedef struct B200Plan B200Plan;   /* opaque; lives behind handle.fft_plan */
 /* Plan for the fused FFT kernels.  n_fft = complex transform length (power of two in
  * [B200_FFT_MIN, B200_FFT_MAX]); x_len/h_len/batch_hint size the staging buffers used when
  * callers pass host pointers.  Aborts on CUDA errors (reference convention: assert). */
-B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len, int n_fft);
+B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len, int n_fft,
+                           int real_packed);
 void b200_plan_destroy(B200Plan *plan);
 int b200_plan_n_fft(const B200Plan *plan);
 float *b200_plan_spectrum(const B200Plan *plan);   /* device pointer */
@@ -54,6 +55,9 @@ void b200_run(B200Plan *plan, int algorithm, const B200Job *job);
 /* transform-length policy (src/selector.c, pure host logic) */
 int b200_os_pick_n(long long h_len, long long out_len);
 int b200_os_part_taps(int n_fft, long long h_len);
+/* full choice: transform length and whether one real segment per transform (real-packed)
+ * beats two paired segments; real-packed needs h_len <= n */
+void b200_os_pick_mode(long long h_len, long long out_len, int *n_fft, int *real_packed);
 
 #define B200_FFT_MIN 256
 #define B200_FFT_MAX 16384

@@ -162,7 +162,7 @@ extern "C" int b200_device_count(void) {
 }
 
 extern "C" B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len,
-                                      int n_fft) {
+                                      int n_fft, int real_packed) {
   B200Plan *plan = new B200Plan();
   plan->magic = 0xB200;
   plan->algorithm = algorithm;
@@ -176,9 +176,13 @@ extern "C" B200Plan *b200_plan_create(int algorithm, long long x_len, long long 
   const bool whole = algorithm == B200_ALG_FFT && x_len + h_len - 1 <= n_fft;
   plan->os.part_taps = whole ? (int)h_len : b200_os_part_taps(n_fft, h_len);
   plan->os.max_parts = (int)((h_len + plan->os.part_taps - 1) / plan->os.part_taps);
+  plan->os.real_packed = real_packed != 0 && !whole && h_len <= n_fft;
+  if (plan->os.real_packed) { plan->os.part_taps = (int)h_len; plan->os.max_parts = 1; }
   plan->os.twiddles = b200_twiddles(n_fft);
+  // paired mode: float2 per bin and partition; real-packed mode: float4 {alpha, beta} per bin
   B200_CUDA_CHECK(cudaMalloc(&plan->os.spectrum,
-                             sizeof(float2) * (size_t)n_fft * plan->os.max_parts));
+                             sizeof(float2) * (size_t)n_fft * plan->os.max_parts *
+                                 (plan->os.real_packed ? 2 : 1)));
   // staging for host-pointer callers is sized now so the call path does not allocate
   {
     const size_t cap = (size_t)16 << 20;     // one pipeline piece at most (see b200_run)
@@ -228,9 +232,10 @@ void launch_device_job(B200Plan *plan, int algorithm, const DevJob &dj, cudaStre
   }
   // handle-less FFT job (extension API with algorithm forced): context-owned scratch
   int dev = current_device();
-  int n = b200_os_pick_n(dj.h_len, dj.out_len);
+  int n = 0, real_packed = 0;
+  b200_os_pick_mode(dj.h_len, dj.out_len, &n, &real_packed);
   int taps = b200_os_part_taps(n, dj.h_len);
-  int parts = (int)((dj.h_len + taps - 1) / taps);
+  int parts = real_packed ? 2 : (int)((dj.h_len + taps - 1) / taps);   // float4 = 2 float2 per bin
   const float2 *tw = b200_twiddles(n);
   std::lock_guard<std::mutex> lock(g_mu);
   DeviceCtx &c = g_ctx[dev];
@@ -240,7 +245,8 @@ void launch_device_job(B200Plan *plan, int algorithm, const DevJob &dj, cudaStre
     B200_CUDA_CHECK(cudaMalloc(&c.spectrum, sizeof(float2) * need));
     c.spectrum_cap = need;
   }
-  b200_os_launch_with(tw, c.spectrum, n, taps, dj, false, stream);
+  if (real_packed) b200_os_launch_real(tw, reinterpret_cast<float4 *>(c.spectrum), n, dj, stream);
+  else b200_os_launch_with(tw, c.spectrum, n, taps, dj, false, stream);
 }
 
 }  // namespace

@@ -41,6 +41,8 @@
 #define FC_HOST_FLOAT2
 struct float2 { float x, y; };
 static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b; return r; }
+struct float4 { float x, y, z, w; };
+static inline float4 make_float4(float a, float b, float c, float d) { float4 r; r.x = a; r.y = b; r.z = c; r.w = d; return r; }
 #endif
 #endif
 
@@ -524,6 +526,284 @@ FC_HD void spec_first(int t, const float *h, i64 start, int dir, int taps,
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
       smb[G::off(k)] = v[k];
+    });
+  });
+}
+
+// ==========================================================================================
+// Real-packed ("mode B") variant: ONE real segment of L = 2N samples per N-point complex
+// transform, z[p] = a[2p] + i*a[2p+1].  Filtering a real sequence with a real impulse
+// response is a real-linear map of z, so in the frequency domain it is widely linear:
+//     Z'[k] = alpha[k] * Z[k] + beta[k] * conj(Z[(N-k) mod N])
+// with  E = Zh[k] + conj(Zh[N-k]),  T = -i * exp(-i*pi*k/N) * (Zh[k] - conj(Zh[N-k])),
+//       alpha = (E - T*sin(pi*k/N)) / 2,   beta = i * T * cos(pi*k/N) / 2,
+// Zh = FFT_N of the impulse response packed the same way (checked numerically against a
+// length-L real FFT convolution; derivation in DESIGN.md).  Compared with the paired mode
+// this yields 2N - taps + 1 outputs per transform instead of 2(N - taps + 1): it pays when
+// the impulse response is long relative to N, at the price of one more shared-memory
+// exchange (each bin needs its mirror bin, which lives in another thread).
+// ==========================================================================================
+
+struct SegReal {
+  const float *x;      // signal base
+  i64 x_len;
+  i64 in0;             // X index of the segment's sample 0 (may be negative)
+  float *out;
+  i64 out0;            // out index receiving circular sample c_off
+  int cnt;             // valid outputs of this segment
+  int c_off;
+  bool accumulate;
+};
+
+// Position of the mirror bin N-k of the bin held in register k3 of centre butterfly
+// (k1 = sub-block, k2 = butterfly inside it).  Bin index k = k1 + R1*k2 + R1*R2*k3.
+template <class P>
+FC_HD int mirror_pos(int k1, int k2, int k3) {
+  constexpr int R2e = P::NPASS == 3 ? P::R2 : 1;
+  int m1, m2, m3;
+  if (k1 > 0) { m1 = P::R1 - k1; m2 = R2e - 1 - k2; m3 = 15 - k3; }
+  else if (k2 > 0) { m1 = 0; m2 = R2e - k2; m3 = 15 - k3; }
+  else { m1 = 0; m2 = 0; m3 = (16 - k3) & 15; }
+  return (m1 * R2e + m2) * 16 + m3;
+}
+
+template <class P>
+FC_HD void centre_locate(int t, int j, int &base, int &bf, int &k1, int &k2) {
+  using G = PassGeom<P, P::R3, P::R3>;
+  int npp;
+  if constexpr (P::NPASS == 3) {
+    G::locate_centre(t, j, base, npp, bf);
+    k1 = bf / P::R2;
+    k2 = bf % P::R2;
+  } else {
+    G::locate(t, j, base, npp, bf);
+    k1 = bf;
+    k2 = 0;
+  }
+}
+
+// first pass, real-packed input
+template <class P>
+FC_HD void fwd_first_real(int t, const SegReal &w, const TwBases<P> &tb, float2 *sm) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  const bool inside = w.in0 >= 0 && w.in0 + 2 * P::N <= w.x_len;
+  // 8-byte loads need an even sample offset from an 8-byte aligned base
+  const bool fast = inside && (((unsigned long long)(w.x + w.in0)) & 7ull) == 0;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
+    float2 v[R];
+    if (fast) {
+      const float2 *xa = reinterpret_cast<const float2 *>(w.x + w.in0) + base;
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        v[bitrev(r, ilog2(R))] = xa[r * G::S];
+      });
+    } else {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const i64 i = w.in0 + 2 * (i64)(base + r * G::S);
+        v[bitrev(r, ilog2(R))] = make_float2(load_x(w.x, w.x_len, i), load_x(w.x, w.x_len, i + 1));
+      });
+    }
+    dft_inreg<R, false>(v);
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tb.w1[j]);
+      static_for<1, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        v[k] = cmul(v[k], pw.template get<k>());
+      });
+    }
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      smb[G::off(k)] = v[k];
+    });
+  });
+}
+
+// centre, step 1: last forward pass, bins written back in place (mirror bins are needed next)
+template <class P>
+FC_HD void centre_real_fwd(int t, float2 *sm) {
+  constexpr int R = P::R3;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    auto *smb = sm + pad_pos(base);
+    float2 v[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = smb[r];
+    });
+    dft_inreg<R, false>(v);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      smb[k] = v[k];
+    });
+  });
+}
+
+// centre, step 2 (after a CTA barrier): Z' = alpha*Z + beta*conj(Z_mirror), then the first
+// inverse pass in registers.  Results stay in u[] until every thread has read its mirrors.
+// AB layout: float4 {alpha, beta} of register k of butterfly j of thread t at (k*T + t)*JB + j.
+template <class P>
+FC_HD void centre_real_mix(int t, const float4 *AB, const float2 *sm, float2 *u) {
+  constexpr int R = P::R3, JB = P::E / R;
+  static_for<0, JB>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    const float2 *smb = sm + pad_pos(base);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      const float2 z = smb[k];
+      const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k))];
+      const float4 ab = AB[(size_t)(k * P::T + t) * JB + j];
+      float2 r = cmul(z, make_float2(ab.x, ab.y));
+      // + beta * conj(zm)
+      r.x = fmaf(ab.z, zm.x, fmaf(ab.w, zm.y, r.x));
+      r.y = fmaf(ab.w, zm.x, fmaf(-ab.z, zm.y, r.y));
+      u[j * R + bitrev(k, ilog2(R))] = r;
+    });
+    dft_inreg<R, true>(u + j * R);
+  });
+}
+
+// centre, step 3 (after a second CTA barrier): write the first inverse pass back
+template <class P>
+FC_HD void centre_real_store(int t, float2 *sm, const float2 *u) {
+  constexpr int R = P::R3;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    auto *smb = sm + pad_pos(base);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      smb[r] = u[j * R + r];
+    });
+  });
+}
+
+// last pass, real-packed output: register r holds circular samples 2p and 2p+1, p = base+r*S
+template <class P>
+FC_HD void inv_last_real(int t, const SegReal &w, const TwBases<P> &tb, const float2 *sm) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
+    float2 v[R];
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tb.w1[j]);
+      static_for<0, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        float2 e = smb[G::off(k)];
+        if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
+        v[bitrev(k, ilog2(R))] = e;
+      });
+    } else {
+      static_for<0, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        v[bitrev(k, ilog2(R))] = smb[G::off(k)];
+      });
+    }
+    dft_inreg<R, true>(v);
+    const int t0 = 2 * base - w.c_off;          // output index of circular sample 2*base
+    float *o = w.out + (w.out0 + t0);           // dereferenced only where 0 <= index < cnt
+    // CTA-uniform: whole pairs, 8-byte aligned, overwrite
+    const bool fast = !w.accumulate && (w.c_off & 1) == 0 && (w.cnt & 1) == 0 &&
+                      (((unsigned long long)(w.out + w.out0)) & 7ull) == 0;
+    if (fast) {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const unsigned tt = (unsigned)(t0 + 2 * r * G::S);
+        if (tt < (unsigned)w.cnt) *reinterpret_cast<float2 *>(o + 2 * r * G::S) = v[r];
+      });
+    } else {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const unsigned tt = (unsigned)(t0 + 2 * r * G::S);
+        float *q = o + 2 * r * G::S;
+        if (tt < (unsigned)w.cnt) q[0] = w.accumulate ? q[0] + v[r].x : v[r].x;
+        if (tt + 1u < (unsigned)w.cnt) q[1] = w.accumulate ? q[1] + v[r].y : v[r].y;
+      });
+    }
+  });
+}
+
+// spectrum side: first pass over the packed, zero-padded impulse response gf[m] = h[start+dir*m]
+template <class P>
+FC_HD void spec_first_real(int t, const float *h, i64 start, int dir, int taps,
+                           const TwBases<P> &tb, float2 *sm) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
+    float2 v[R];
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const int m = 2 * (base + r * G::S);
+      const float a = m < taps ? h[start + (i64)dir * m] : 0.0f;
+      const float b = m + 1 < taps ? h[start + (i64)dir * (m + 1)] : 0.0f;
+      v[bitrev(r, ilog2(R))] = make_float2(a, b);
+    });
+    dft_inreg<R, false>(v);
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tb.w1[j]);
+      static_for<1, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        v[k] = cmul(v[k], pw.template get<k>());
+      });
+    }
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      smb[G::off(k)] = v[k];
+    });
+  });
+}
+
+// spectrum side, after centre_real_fwd + CTA barrier: alpha / beta of every bin
+template <class P>
+FC_HD void centre_real_coeffs(int t, float4 *AB, float scale, const float2 *sm) {
+  constexpr int R = P::R3, JB = P::E / R;
+  constexpr int R2e = P::NPASS == 3 ? P::R2 : 1;
+  static_for<0, JB>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    const float2 *smb = sm + pad_pos(base);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k3 = decltype(kk)::value;
+      const float2 z = smb[k3];
+      const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k3))];
+      const int kbin = k1 + P::R1 * (k2 + R2e * k3);
+      float sn, cs;
+#if defined(__CUDA_ARCH__)
+      sincospif((float)kbin / (float)P::N, &sn, &cs);
+#else
+      sn = (float)sin(3.14159265358979323846 * kbin / P::N);
+      cs = (float)cos(3.14159265358979323846 * kbin / P::N);
+#endif
+      const float2 e = make_float2(z.x + zm.x, z.y - zm.y);      // Z + conj(Zm)
+      const float2 d = make_float2(z.x - zm.x, z.y + zm.y);      // Z - conj(Zm)
+      // T = -i * (cs - i*sn) * d = (-sn - i*cs) * d
+      const float2 tt = cmul(make_float2(-sn, -cs), d);
+      const float2 al = make_float2(0.5f * scale * (e.x - tt.x * sn), 0.5f * scale * (e.y - tt.y * sn));
+      // beta = i * T * cs / 2
+      const float2 be = make_float2(-0.5f * scale * tt.y * cs, 0.5f * scale * tt.x * cs);
+      AB[(size_t)(k3 * P::T + t) * JB + j] = make_float4(al.x, al.y, be.x, be.y);
     });
   });
 }

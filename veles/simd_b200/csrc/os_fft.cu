@@ -159,6 +159,93 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
   if (live) inv_last<P>(t, w, tb, sm);
 }
 
+// ---- real-packed mode (fft_core.cuh, "mode B"): one real segment of 2N samples per CTA ------
+template <class P>
+__global__ void __launch_bounds__(P::T) os_spectrum_real_kernel(SpecParams p) {
+  extern __shared__ float4 smem4[];
+  float2 *sm = reinterpret_cast<float2 *>(smem4);
+  const int t = threadIdx.x;
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // single partition: convolution-form impulse response gf[m] = reverse ? h[taps-1-m] : h[m]
+  const int taps = (int)p.h_len;
+  const i64 start = p.reverse ? taps - 1 : 0;
+  const int dir = p.reverse ? -1 : 1;
+  TwBases<P> tb;
+  load_twiddle_bases<P>(t, p.tw, tb);
+  spec_first_real<P>(t, p.h, start, dir, taps, tb, sm);
+  __syncthreads();
+  if constexpr (P::NPASS == 3) {
+    fwd_mid<P>(t, tb, sm);
+    __syncthreads();
+  }
+  centre_real_fwd<P>(t, sm);
+  __syncthreads();
+  centre_real_coeffs<P>(t, reinterpret_cast<float4 *>(p.spectrum), p.scale, sm);
+}
+
+template <class P, int G>
+__global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
+  extern __shared__ float4 smem4[];
+  const int grp = threadIdx.x / P::T;
+  const int t = threadIdx.x % P::T;
+  float2 *sm = reinterpret_cast<float2 *>(smem4) + grp * P::SMEM_FLOAT2;
+
+  const i64 item = (i64)blockIdx.x * G + grp;
+  const bool live = item < p.total;
+  SegReal w;
+  TwBases<P> tb;
+  float2 u[P::E];
+  if (t == 0) {
+    const i64 nxt = item + p.prefetch_distance;
+    if (p.prefetch_distance > 0 && nxt < p.total) {
+      const i64 nb = nxt / p.nseg;
+      i64 lo = (nxt % p.nseg) * p.step + p.in_shift;
+      i64 hi = lo + 2 * P::N;
+      if (lo < 0) lo = 0;
+      if (hi > p.x_len) hi = p.x_len;
+      const float *base = p.x + nb * p.x_stride;
+      unsigned long long a0 = ((unsigned long long)(base + lo) + 15ull) & ~15ull;
+      unsigned long long a1 = (unsigned long long)(base + hi) & ~15ull;
+      if (a1 > a0) {
+        unsigned bytes = (unsigned)(a1 - a0);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"(bytes) : "memory");
+      }
+    }
+  }
+  if (live) {
+    load_twiddle_bases<P>(t, p.tw, tb);
+    const i64 b = item / p.nseg;
+    const i64 sg = item % p.nseg;
+    w.x = p.x + b * p.x_stride;
+    w.x_len = p.x_len;
+    w.in0 = sg * p.step + p.in_shift;
+    w.out = p.out + b * p.out_stride;
+    w.out0 = sg * p.step;
+    const i64 rem = p.out_len - w.out0;
+    w.cnt = (int)(rem < p.step ? rem : p.step);
+    w.c_off = p.c_off;
+    w.accumulate = p.accumulate != 0;
+    fwd_first_real<P>(t, w, tb, sm);
+  }
+  __syncthreads();
+  if constexpr (P::NPASS == 3) {
+    if (live) fwd_mid<P>(t, tb, sm);
+    __syncwarp();                       // middle passes stay inside the half-warp
+  }
+  if (live) centre_real_fwd<P>(t, sm);
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  __syncthreads();                      // mirror bins live in other warps
+  if (live) centre_real_mix<P>(t, reinterpret_cast<const float4 *>(p.spectrum), sm, u);
+  __syncthreads();                      // every mirror has been read: safe to overwrite
+  if (live) centre_real_store<P>(t, sm, u);
+  if constexpr (P::NPASS == 3) {
+    __syncwarp();
+    if (live) inv_mid<P>(t, tb, sm);
+  }
+  __syncthreads();
+  if (live) inv_last_real<P>(t, w, tb, sm);
+}
+
 // ---- plan table ---------------------------------------------------------------------------
 // N         radices      E   threads/transform   transforms per CTA
 using P256 = Plan<256, 16, 16, 1, 16>;      // 16                8
@@ -169,15 +256,15 @@ using P4096 = Plan<4096, 16, 16, 16, 16>;   // 256               1
 using P8192 = Plan<8192, 32, 32, 16, 16>;   // 256               1
 using P16384 = Plan<16384, 32, 32, 32, 16>; // 512               1
 
-template <class P, int G>
+template <class P, int G, bool REAL>
 void launch_fused(const OsParams &p, cudaStream_t stream, bool after_spectrum) {
+  auto kernel = REAL ? os_fused_real_kernel<P, G> : os_fused_kernel<P, G>;
   static bool configured[16] = {false};
   size_t smem = sizeof(float2) * P::SMEM_FLOAT2 * G;
   int dev = 0;
   B200_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 16 && !configured[dev]) {
-    B200_CUDA_CHECK(cudaFuncSetAttribute(os_fused_kernel<P, G>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured[dev] = true;
   }
   i64 blocks = (p.total + G - 1) / G;
@@ -189,8 +276,7 @@ void launch_fused(const OsParams &p, cudaStream_t stream, bool after_spectrum) {
     static int wave[16] = {0};
     if (dev < 16 && wave[dev] == 0) {
       int per_sm = 0, sms = 0;
-      B200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, os_fused_kernel<P, G>,
-                                                                    P::T * G, smem));
+      B200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, P::T * G, smem));
       B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
       wave[dev] = per_sm * sms > 0 ? per_sm * sms : 1;
     }
@@ -208,28 +294,28 @@ void launch_fused(const OsParams &p, cudaStream_t stream, bool after_spectrum) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, os_fused_kernel<P, G>, q));
+    B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, q));
   } else {
-    os_fused_kernel<P, G><<<(unsigned)blocks, P::T * G, smem, stream>>>(q);
+    kernel<<<(unsigned)blocks, P::T * G, smem, stream>>>(q);
   }
   b200_prof_end(B200_PROF_FUSED, stream);
   B200_CUDA_CHECK(cudaGetLastError());
   b200_count_launch(1);
 }
 
-template <class P>
+template <class P, bool REAL>
 void launch_spectrum(const SpecParams &p, int parts, cudaStream_t stream) {
+  auto kernel = REAL ? os_spectrum_real_kernel<P> : os_spectrum_kernel<P>;
   static bool configured[16] = {false};
   size_t smem = sizeof(float2) * P::SMEM_FLOAT2;
   int dev = 0;
   B200_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 16 && !configured[dev]) {
-    B200_CUDA_CHECK(cudaFuncSetAttribute(os_spectrum_kernel<P>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured[dev] = true;
   }
   b200_prof_begin(B200_PROF_SPECTRUM, stream);
-  os_spectrum_kernel<P><<<parts, P::T, smem, stream>>>(p);
+  kernel<<<parts, P::T, smem, stream>>>(p);
   b200_prof_end(B200_PROF_SPECTRUM, stream);
   B200_CUDA_CHECK(cudaGetLastError());
   b200_count_launch(1);
@@ -284,7 +370,7 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
 
 #define B200_DISPATCH(PLAN, GROUPS)                                                    \
   case PLAN::N: {                                                                      \
-    launch_spectrum<PLAN>(sp, parts, stream);                                          \
+    launch_spectrum<PLAN, false>(sp, parts, stream);                                   \
     for (int q = 0; q < parts; q++) {                                                  \
       const i64 j0 = (i64)q * part_taps;                                               \
       const i64 left = job.h_len - j0;                                                 \
@@ -303,7 +389,7 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
       op.nseg = (job.out_len + op.step - 1) / op.step;                                 \
       op.npairs = (op.nseg + 1) / 2;                                                   \
       op.total = op.npairs * job.batch;                                                \
-      launch_fused<PLAN, GROUPS>(op, stream, q == 0);                                  \
+      launch_fused<PLAN, GROUPS, false>(op, stream, q == 0);                           \
     }                                                                                  \
   } break;
 
@@ -321,8 +407,59 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
 #undef B200_DISPATCH
 }
 
+// Real-packed mode: one real segment of 2*n_fft samples per CTA, all taps in one partition
+// (h_len <= n_fft).  `coeffs` holds n_fft float4 {alpha, beta}.
+void b200_os_launch_real(const float2 *tw, float4 *coeffs, int n_fft, const DevJob &job,
+                         cudaStream_t stream) {
+  if (job.batch <= 0 || job.out_len <= 0) return;
+  B200_REQUIRE(job.h_len <= n_fft, "real-packed mode needs all taps in one transform");
+  SpecParams sp;
+  sp.h = job.h; sp.h_len = job.h_len; sp.reverse = job.reverse;
+  sp.part_taps = (int)job.h_len; sp.spectrum = reinterpret_cast<float2 *>(coeffs); sp.tw = tw;
+  sp.scale = 1.0f / (float)n_fft;
+
+  OsParams op;
+  op.x = job.x; op.x_len = job.x_len; op.x_stride = job.x_stride;
+  op.out = job.out; op.out_len = job.out_len; op.out_stride = job.out_stride;
+  op.tw = tw;
+  op.spectrum = reinterpret_cast<const float2 *>(coeffs);
+  op.accumulate = 0;
+  // one extra leading sample when pad is odd keeps segment starts on even sample offsets
+  // (8-byte loads of sample pairs) and makes the first useful circular sample even
+  const int e = (int)(job.pad & 1);
+  op.in_shift = -job.pad - e;
+  op.c_off = (int)job.h_len - 1 + e;
+  op.step = (2 * n_fft - op.c_off) & ~1;
+  op.nseg = (job.out_len + op.step - 1) / op.step;
+  op.npairs = op.nseg;
+  op.total = op.nseg * job.batch;
+
+#define B200_DISPATCH_REAL(PLAN, GROUPS)                       \
+  case PLAN::N:                                                \
+    launch_spectrum<PLAN, true>(sp, 1, stream);                \
+    launch_fused<PLAN, GROUPS, true>(op, stream, true);        \
+    break;
+  switch (n_fft) {
+    B200_DISPATCH_REAL(P256, 8)
+    B200_DISPATCH_REAL(P512, 4)
+    B200_DISPATCH_REAL(P1024, 2)
+    B200_DISPATCH_REAL(P2048, 1)
+    B200_DISPATCH_REAL(P4096, 1)
+    B200_DISPATCH_REAL(P8192, 1)
+    B200_DISPATCH_REAL(P16384, 1)
+    default:
+      B200_REQUIRE(false, "unsupported transform length");
+  }
+#undef B200_DISPATCH_REAL
+}
+
 void b200_os_launch(const OsDevPlan &plan, const DevJob &job, bool single_segment,
                     cudaStream_t stream) {
+  if (plan.real_packed && !single_segment) {
+    b200_os_launch_real(plan.twiddles, reinterpret_cast<float4 *>(plan.spectrum), plan.n_fft, job,
+                        stream);
+    return;
+  }
   const int parts = (int)((job.h_len + plan.part_taps - 1) / plan.part_taps);
   B200_REQUIRE(parts <= plan.max_parts, "impulse response longer than the plan was sized for");
   b200_os_launch_with(plan.twiddles, plan.spectrum, plan.n_fft, plan.part_taps, job,

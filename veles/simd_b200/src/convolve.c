@@ -58,8 +58,10 @@ ConvolutionOverlapSaveHandle convolve_overlap_save_initialize(size_t xLength,
   SIMD_REQUIRE(hLength > 0);
   ConvolutionOverlapSaveHandle handle;
   memset(&handle, 0, sizeof(handle));
-  int n = b200_os_pick_n((long long)hLength, (long long)(xLength + hLength - 1));
-  B200Plan *plan = b200_plan_create(B200_ALG_OS, (long long)xLength, (long long)hLength, n);
+  int n = 0, real_packed = 0;
+  b200_os_pick_mode((long long)hLength, (long long)(xLength + hLength - 1), &n, &real_packed);
+  B200Plan *plan = b200_plan_create(B200_ALG_OS, (long long)xLength, (long long)hLength, n,
+                                    real_packed);
   handle.fft_plan = plan;
   handle.fft_inverse_plan = plan;
   handle.fft_boiler_plate = b200_plan_scratch(plan);
@@ -106,13 +108,14 @@ ConvolutionFFTHandle convolve_fft_initialize(size_t xLength, size_t hLength) {
   handle.h_length = (int)hLength;
   handle.reverse = 0;
   handle.inputs = NULL;
-  int n;
+  int n, real_packed = 0;
   if (out_len <= B200_FFT_MAX) {
     n = (int)(M < B200_FFT_MIN ? B200_FFT_MIN : M);   /* whole signal in one transform */
   } else {
-    n = b200_os_pick_n((long long)hLength, out_len);  /* partitioned transforms */
+    b200_os_pick_mode((long long)hLength, out_len, &n, &real_packed);  /* segmented / partitioned */
   }
-  B200Plan *plan = b200_plan_create(B200_ALG_FFT, (long long)xLength, (long long)hLength, n);
+  B200Plan *plan = b200_plan_create(B200_ALG_FFT, (long long)xLength, (long long)hLength, n,
+                                    real_packed);
   handle.fft_plan = plan;
   handle.fft_inverse_plan = plan;
   return handle;

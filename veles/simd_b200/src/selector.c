@@ -60,6 +60,37 @@ int b200_os_pick_n(long long h_len, long long out_len) {
   return best;
 }
 
+/* Real-packed mode: one real segment of 2N samples per N-point transform.  Its transform
+ * costs B200_REAL_COST_RATIO times the paired one (one more shared-memory exchange, two more
+ * barriers) but yields 2N - taps + 1 outputs instead of 2(N - taps + 1). */
+#define B200_REAL_COST_RATIO 1.25   /* measured on C4 / C5: 1.24 */
+
+static double real_cost_us(int n, double c, long long h_len, long long out_len, long long batch) {
+  double step = (double)(2 * n - (h_len - 1) - 1);
+  double nseg = (double)((out_len + (long long)step - 1) / (long long)step);
+  return B200_FUSED_LAUNCH_US + B200_REAL_COST_RATIO * c * nseg * 2.0 * n * (double)batch / 67.1e6;
+}
+
+void b200_os_pick_mode(long long h_len, long long out_len, int *n_fft, int *real_packed) {
+  int n_a = b200_os_pick_n(h_len, out_len);
+  *n_fft = n_a;
+  *real_packed = 0;
+  const char *force = getenv("VELES_B200_REAL");        /* tuning knob: 0 / 1 */
+  if (force && atoi(force) == 0) return;
+  double best = 1e300;
+  for (unsigned i = 0; i < sizeof(kFusedCost) / sizeof(kFusedCost[0]); i++)
+    if (kFusedCost[i].n == n_a) best = fused_cost_us(n_a, kFusedCost[i].c, h_len, out_len, 1);
+  if (force && atoi(force) == 1) best = 1e300;
+  const char *force_n = getenv("VELES_B200_FORCE_N");
+  for (unsigned i = 0; i < sizeof(kFusedCost) / sizeof(kFusedCost[0]); i++) {
+    int n = kFusedCost[i].n;
+    if (h_len > n) continue;                            /* all taps in one transform */
+    if (force_n && atoi(force_n) != n) continue;
+    double cost = real_cost_us(n, kFusedCost[i].c, h_len, out_len, 1);
+    if (cost < best * 0.98) { best = cost; *n_fft = n; *real_packed = 1; }
+  }
+}
+
 /* Handle-time decision for `batch` signals (the reference API has no batch: batch = 1). */
 ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_length,
                                                       size_t batch) {
