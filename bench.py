@@ -237,6 +237,8 @@ def main():
         flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     handle = v.Handle(x_len, h_len, "", corr)
+    if args.algorithm == 0:
+        os.environ["VELES_B200_NO_BATCH_CROSSOVER"] = "1"
     if args.algorithm >= 0 and args.algorithm != handle.algorithm:
         handle.close()
         handle = ForcedHandle(v, x_len, h_len, corr, args.algorithm)

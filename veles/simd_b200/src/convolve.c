@@ -211,7 +211,9 @@ static void batch_dispatch(ConvolutionHandle handle, const float *x, size_t x_st
       /* The handle was chosen for one signal.  A large batch can cross over to the fused
        * transform kernels (profiles/selector_sweep_r01.md); those then run without a handle,
        * on the per-device context's scratch. */
-      if (simd_b200_select_algorithm_batch(xl, hl, batch) == kConvolutionAlgorithmBruteForce) {
+      /* profiling knob: VELES_B200_NO_BATCH_CROSSOVER=1 keeps the batch on the direct kernel */
+      if (getenv("VELES_B200_NO_BATCH_CROSSOVER") ||
+          simd_b200_select_algorithm_batch(xl, hl, batch) == kConvolutionAlgorithmBruteForce) {
         run_full(NULL, B200_ALG_DIRECT, x, xl, x_stride, h, hl, result, result_stride, batch,
                  brute_reverse);
       } else {
