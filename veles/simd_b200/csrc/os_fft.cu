@@ -246,6 +246,159 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
   if (live) inv_last_real<P>(t, w, tb, sm);
 }
 
+// ---- persistent variant of the paired kernel for the one-CTA-per-SM plans ------------------
+// One CTA per SM loops over segment pairs.  While a pair is being transformed, a bulk
+// asynchronous copy (cp.async.bulk / TMA, completion on an mbarrier) brings the next pair's
+// input range into the shared memory left over beside the transform buffer, so the next
+// pair's first pass starts from shared memory instead of waiting for HBM, and the current
+// pair's result stores drain while that first pass computes.  Needs 16-byte aligned segment
+// starts (the host picks step and leading-sample count accordingly) -- otherwise, and for
+// pairs that stick out of the signal, the plain kernel's guarded loads are used.
+constexpr int kParkFloats = 20992;      // 82 KiB beside the 136 KiB transform buffer (+ 8 KiB twiddle bases)
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned bytes,
+                                          unsigned long long *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile(
+        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+
+template <class P>
+__global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
+  extern __shared__ float4 smem4[];
+  float2 *sm = reinterpret_cast<float2 *>(smem4);
+  float *park = reinterpret_cast<float *>(sm + P::SMEM_FLOAT2);
+  TwBases<P> *tb_sm = reinterpret_cast<TwBases<P> *>(park + kParkFloats);   // one per thread
+  unsigned long long *bar = reinterpret_cast<unsigned long long *>(tb_sm + P::T);
+  const int t = threadIdx.x;
+
+  // parked range of a pair: x[inA, inA + park_len), clipped to what the pair reads
+  const int need = P::N + p.step;                       // A followed by B's tail
+  const int park_len = need < kParkFloats ? need : kParkFloats;
+
+  auto pair_of = [&](i64 item, SegPair &w) {
+    const i64 b = item / p.npairs;
+    const i64 sa = (item % p.npairs) * 2;
+    w.x = p.x + b * p.x_stride;
+    w.x_len = p.x_len;
+    w.inA = sa * p.step + p.in_shift;
+    w.inB = w.inA + p.step;
+    w.haveB = sa + 1 < p.nseg;
+    w.out = p.out + b * p.out_stride;
+    w.outA = sa * p.step;
+    w.outB = w.outA + p.step;
+    const i64 remA = p.out_len - w.outA, remB = p.out_len - w.outB;
+    w.cntA = (int)(remA < p.step ? remA : p.step);
+    w.cntB = w.haveB ? (int)(remB < p.step ? remB : p.step) : 0;
+    w.c_off = p.c_off;
+    w.accumulate = p.accumulate != 0;
+  };
+  // a pair can be parked when everything it reads lies inside the signal
+  auto parkable = [&](const SegPair &w) {
+    return w.haveB && w.inA >= 0 && w.inB + P::N <= w.x_len;
+  };
+  auto issue_park = [&](const SegPair &w) {             // one thread
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    const unsigned bytes = (unsigned)park_len * 4u;
+    mbar_expect_tx(bar, bytes);
+    const char *src = reinterpret_cast<const char *>(w.x + w.inA);
+    char *dst = reinterpret_cast<char *>(park);
+    for (unsigned off = 0; off < bytes; off += 32768u) {
+      const unsigned n = bytes - off < 32768u ? bytes - off : 32768u;
+      bulk_load(dst + off, src + off, n, bar);
+    }
+  };
+
+  if (t == 0) mbar_init(bar, 1);
+  {
+    TwBases<P> tb0;
+    load_twiddle_bases<P>(t, p.tw, tb0);
+    tb_sm[t] = tb0;             // read back by the same thread only
+  }
+  __syncthreads();
+  HRegs<P> hr;
+
+  // Loop state is kept small on purpose (the passes need ~124 registers): the pair
+  // descriptor is recomputed where it is needed instead of being carried across phases.
+  int item = blockIdx.x;
+  bool parked = false;
+  if (item < p.total) {
+    SegPair w0;
+    pair_of(item, w0);
+    parked = parkable(w0);
+    if (parked && t == 0) issue_park(w0);
+  }
+  unsigned parity = 0;
+  asm volatile("griddepcontrol.wait;" ::: "memory");     // the spectrum kernel is short
+  for (; item < p.total; item += gridDim.x) {
+    {
+      SegPair w;
+      pair_of(item, w);
+      const TwBases<P> tb = tb_sm[t];
+      if (parked) {
+        mbar_wait(bar, parity);
+        parity ^= 1u;
+        fwd_first_parked<P>(t, w, tb, sm, park, park_len, p.step);
+      } else {
+        fwd_first<P>(t, w, tb, sm);
+      }
+    }
+    __syncthreads();            // first-pass results visible; the parked range is consumed
+    // start fetching the next pair's input while this pair is transformed
+    {
+      const i64 nxt = (i64)item + gridDim.x;
+      parked = false;
+      if (nxt < p.total) {
+        SegPair wn;
+        pair_of(nxt, wn);
+        parked = parkable(wn);
+        if (parked && t == 0) issue_park(wn);
+      }
+    }
+    if constexpr (P::NPASS == 3) {
+      { const TwBases<P> tb = tb_sm[t]; fwd_mid<P>(t, tb, sm); }
+      load_spectrum<P>(t, p.spectrum, hr);
+      __syncwarp();
+      centre<P>(t, hr, sm);
+      __syncwarp();
+      { const TwBases<P> tb = tb_sm[t]; inv_mid<P>(t, tb, sm); }
+    } else {
+      load_spectrum<P>(t, p.spectrum, hr);
+      centre<P>(t, hr, sm);
+    }
+    __syncthreads();
+    {
+      SegPair w;
+      pair_of(item, w);
+      const TwBases<P> tb = tb_sm[t];
+      inv_last<P>(t, w, tb, sm);
+    }
+    // the next first pass writes only positions this thread has just read: no barrier here
+  }
+}
+
 // ---- plan table ---------------------------------------------------------------------------
 // N         radices      E   threads/transform   transforms per CTA
 using P256 = Plan<256, 16, 16, 1, 16>;      // 16                8
@@ -321,6 +474,55 @@ void launch_spectrum(const SpecParams &p, int parts, cudaStream_t stream) {
   b200_count_launch(1);
 }
 
+// Persistent launch of the 16384-point paired plan (see os_fused_persist_kernel).
+bool launch_persist_16384(OsParams op, const DevJob &job, i64 j0, int taps, cudaStream_t stream,
+                          bool after_spectrum) {
+  using PLAN = P16384;
+  if (getenv("VELES_B200_NO_PERSIST")) return false;
+  if ((((unsigned long long)job.x) & 15ull) != 0 || (job.x_stride & 3) != 0) return false;
+  // leading extra samples so that every segment starts on a 16-byte boundary
+  const i64 shift = j0 - job.pad;
+  const int e = (int)(((shift % 4) + 4) % 4);
+  op.in_shift = shift - e;
+  op.c_off = taps - 1 + e;
+  op.step = (PLAN::N - op.c_off) & ~3;
+  if (op.step < PLAN::N / 4) return false;
+  op.nseg = (job.out_len + op.step - 1) / op.step;
+  op.npairs = (op.nseg + 1) / 2;
+  op.total = op.npairs * job.batch;
+  op.prefetch_distance = 0;
+  static bool configured[16] = {false};
+  static int sms[16] = {0};
+  if (op.total >= 2147483647LL) return false;
+  const size_t smem = sizeof(float2) * PLAN::SMEM_FLOAT2 + sizeof(float) * kParkFloats +
+                      sizeof(fc::TwBases<PLAN>) * PLAN::T + 16;
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev >= 16) return false;
+  if (!configured[dev]) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(os_fused_persist_kernel<PLAN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
+    configured[dev] = true;
+  }
+  i64 blocks = op.total < sms[dev] ? op.total : sms[dev];
+  b200_prof_begin(B200_PROF_FUSED, stream);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)blocks);
+  cfg.blockDim = dim3(PLAN::T);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = after_spectrum ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, os_fused_persist_kernel<PLAN>, op));
+  b200_prof_end(B200_PROF_FUSED, stream);
+  b200_count_launch(1);
+  return true;
+}
+
 struct TwiddleCache {
   std::mutex mu;
   const float2 *tab[16][16] = {};   // [device][log2 n]
@@ -389,6 +591,9 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
       op.nseg = (job.out_len + op.step - 1) / op.step;                                 \
       op.npairs = (op.nseg + 1) / 2;                                                   \
       op.total = op.npairs * job.batch;                                                \
+      if (PLAN::N == 16384 && !single_segment && parts == 1 &&                         \
+          launch_persist_16384(op, job, j0, taps, stream, q == 0))                     \
+        continue;                                                                      \
       launch_fused<PLAN, GROUPS, false>(op, stream, q == 0);                           \
     }                                                                                  \
   } break;
