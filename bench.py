@@ -198,6 +198,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--out-row-align", type=int, default=1,
+                    help="pad result rows to a multiple of this many floats (experiment)")
     ap.add_argument("--no-profile", action="store_true",
                     help="do not bracket kernels with events (they sit between the two launches of a step)")
     ap.add_argument("--min-warm-s", type=float, default=0.6,
@@ -230,7 +232,11 @@ def main():
     g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
     x = torch.rand((batch, x_len), generator=g, device="cuda") * 2 - 1
     h = torch.rand((h_len,), generator=g, device="cuda") * 2 - 1
-    y = torch.empty((batch, out_len), device="cuda")
+    if args.out_row_align > 1:
+        pitch = -(-out_len // args.out_row_align) * args.out_row_align
+        y = torch.empty((batch, pitch), device="cuda")[:, :out_len]
+    else:
+        y = torch.empty((batch, out_len), device="cuda")
     flush = None
     in_bytes = x.numel() * 4
     if in_bytes < 256 << 20:            # inputs smaller than L2 (126 MB): flush between steps

@@ -141,7 +141,8 @@ def _is_torch(a):
 def _ptr(a):
     """Raw address of a numpy array (host) or torch tensor (host or device)."""
     if _is_torch(a):
-        assert a.dtype.is_floating_point and a.element_size() == 4 and a.is_contiguous()
+        # 1-D contiguous, or 2-D with contiguous rows (row stride is passed separately)
+        assert a.dtype.is_floating_point and a.element_size() == 4 and a.stride(-1) == 1
         return a.data_ptr()
     assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
     return a.ctypes.data
