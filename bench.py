@@ -40,6 +40,8 @@ WORKLOADS = {
     "c3": ("convolve", 4096, 16384, 64, "batched convolve 4096 x 16384, h=64"),
     "c4": ("convolve", 1024, 262144, 4096, "batched convolve 1024 x 262144, h=4096"),
     "c5": ("convolve", 1, 2 ** 30, 8192, "single long signal x=2^30, h=8192"),
+    # SURVEY 8(f) rank 1 (not a BASELINE config): extrema of a 2^28-sample series
+    "peaks": ("detect_peaks", 1, 2 ** 28, 0, "detect_peaks (both kinds) on 2^28 uniform random samples"),
 }
 FP32_PEAK_TFLOPS = 72.1   # measured on this pool's B200 (tools/ffma_peak, profiles/ffma_peak_r01.json)
 
@@ -229,6 +231,8 @@ def main():
     out_len = x_len + h_len - 1
     if args.workload == "c5" and world > 1:
         return run_sharded_long_signal(args, v, world, rank, local)
+    if args.workload == "peaks":
+        return run_detect_peaks(args, v, world, rank)
     g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
     x = torch.rand((batch, x_len), generator=g, device="cuda") * 2 - 1
     h = torch.rand((h_len,), generator=g, device="cuda") * 2 - 1
@@ -445,6 +449,60 @@ def run_sharded_long_signal(args, v, world, rank, local):
                 "e2e": None, "roofline": None, "cpu_baseline": None, "clocks": None}
         print(json.dumps(line), flush=True)
     dist.destroy_process_group()
+
+
+def run_detect_peaks(args, v, world, rank):
+    """detect_peaks, device-resident: value = input samples/s; roofline on the algorithmic
+    bytes 4*size (series read once) + 8*peaks (list written once) of the whole three-kernel
+    call, timed with CUDA events on the launching stream."""
+    import numpy as np
+    import torch
+    _, _, size, _, desc = WORKLOADS["peaks"]
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
+    data = torch.rand((size,), generator=g, device="cuda") * 2 - 1
+    out = torch.empty((size, 2), dtype=torch.int32, device="cuda")
+    for _ in range(args.warmup):
+        n = v.detect_peaks_device(data, out, 3)
+    torch.cuda.synchronize()
+    launches0 = v.lib.simd_b200_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        n = v.detect_peaks_device(data, out, 3)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    peaks, _ = load_peaks()
+    abytes = 4.0 * size + 8.0 * n
+    ach = abytes / (ms * 1e-3) / 1e9
+    base = None
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from _oracle import Oracle, Reference, have_reference
+        sample = (np.random.default_rng(1).uniform(-1, 1, 2 ** 24)).astype(np.float32)
+        impl, kind = (Reference(), "reference") if have_reference() else (Oracle(), "port")
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 2.0:
+            impl.lib.detect_peaks if kind == "reference" else None
+            (impl.detect_peaks(sample[: 2 ** 20], 3, 1) if kind == "reference" else impl.detect_peaks(sample[: 2 ** 20], 3))
+            reps += 1
+        dt = time.perf_counter() - t0
+        base = {"value": reps * 2 ** 20 / dt / 1e9, "unit": "GSamples/s", "cores": 1, "kind": kind,
+                "sample": f"2^20-sample prefix, {reps} repetitions in {dt:.2f} s, single thread "
+                          "(the reference is single-threaded; includes the ctypes result copy)"}
+    line = {"metric": "detect_peaks_input_gsamples_per_s", "value": size / (ms * 1e-3) / 1e9,
+            "unit": "GSamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"peaks: {desc}", "extrema_found": int(n), "l2": "inputs larger than L2"},
+            "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0), "e2e": None,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": ach / peaks["hbm_gbs"], "traffic": None,
+                         "kernel": "peaks_count + peaks_scan + peaks_write (whole call)",
+                         "algorithmic_bytes_per_launch": abytes},
+            "cpu_baseline": base, "clocks": None}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
 
 
 class ForcedHandle:

@@ -93,6 +93,26 @@ x, h = uni(77, 300), uni(78, 128)
 add("q1_300x128_convolve_auto", x, h, "convolve", "auto", guard=4096)
 add("q1_300x128_convolve_simd0", x, h, "convolve", "simd0")
 
+# --- detect_peaks: reference scalar path, tests/detect_peaks.cc:43-100
+peaks = {}
+sin_series = np.sin((np.arange(4000) * np.pi / 100).astype(np.float32).astype(np.float64)).astype(np.float32)
+nasty = np.zeros(101, dtype=np.float32)
+nasty[[7, 16, 97, 99]] = 1
+noise = uni(4242, 100000)
+corr = cases["c2_correlate_simd0"]["y"]
+for pname, series in (("sin", sin_series), ("nasty", nasty), ("noise", noise), ("corr_c2", corr),
+                      ("tiny3", np.array([0, 1, 0], np.float32)), ("flat", np.ones(50, np.float32))):
+    peaks[pname + "/data"] = series
+    for t in (1, 2, 3):
+        pos, val = ref.detect_peaks(series, t, simd=0)
+        peaks[f"{pname}/pos{t}"] = pos
+        peaks[f"{pname}/val{t}"] = val
+assert peaks["sin/pos1"].tolist() == [i * 200 + 50 for i in range(20)]
+assert peaks["nasty/pos1"].tolist() == [7, 16, 97, 99]
+pdst = os.path.join(os.path.dirname(HERE), "tests", "golden", "peaks.npz")
+np.savez_compressed(pdst, **peaks)
+print(f"wrote {pdst}: {os.path.getsize(pdst)/1e6:.2f} MB")
+
 out = {}
 index = []
 for name, c in cases.items():

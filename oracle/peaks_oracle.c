@@ -1,0 +1,25 @@
+/* oracle/peaks_oracle.c -- TEST INFRASTRUCTURE, not product code.
+ * CPU restatement of detect_peaks (scalar path), /root/reference/src/detect_peaks.c:41-56
+ * (check_peak) and :118-125 (the simd == 0 loop).  Parity status: PINNED against the
+ * reference's own tests (tests/detect_peaks.cc:43-100: sin and nasty_peaks) and against the
+ * reference's source compiled into oracle/_ref (bit-exact, simd = 0).
+ * Output: positions[i], values[i] for the first `capacity` extrema; returns the total found.
+ */
+#include <stddef.h>
+
+__attribute__((visibility("default")))
+size_t oracle_detect_peaks(const float *data, size_t size, int type, int *positions,
+                           float *values, size_t capacity) {
+  size_t n = 0;
+  for (long i = 1; i < (long)size - 1; i++) {            /* :118-125 */
+    float prev = data[i - 1], curr = data[i], next = data[i + 1];
+    float delta1 = curr - prev, delta2 = curr - next;    /* :47-48 */
+    if (delta1 * delta2 > 0) {                           /* :49 */
+      if ((delta1 > 0 && (type & 1) != 0) || (delta1 < 0 && (type & 2) != 0)) {   /* :50-51 */
+        if (n < capacity) { positions[n] = (int)i; values[n] = curr; }
+        n++;
+      }
+    }
+  }
+  return n;
+}

@@ -48,6 +48,8 @@ class Oracle:
         L.oracle_cross_correlate.argtypes = [_fp, sz, _fp, sz, _fp]
         L.oracle_convolve_batch.argtypes = [_fp, sz, sz, _fp, sz, _fp, sz, sz, C.c_int, C.c_int]
         L.oracle_convolve_batch.restype = C.c_int
+        L.oracle_detect_peaks.argtypes = [_fp, sz, C.c_int, C.POINTER(C.c_int), _fp, sz]
+        L.oracle_detect_peaks.restype = sz
 
     def _run(self, fn, x, h, *extra):
         x, xp = _f32(x)
@@ -80,6 +82,16 @@ class Oracle:
         out = np.empty(x.size + h.size - 1, dtype=np.float64)
         self.lib.oracle_convolve_f64(xp, x.size, hp, h.size, int(reverse), out.ctypes.data_as(_dp))
         return out
+
+    def detect_peaks(self, data, type_=3):
+        """(positions int32[], values float32[]) of the scalar reference loop."""
+        d, dp = _f32(data)
+        cap = max(d.size, 1)
+        pos = np.empty(cap, dtype=np.int32)
+        val = np.empty(cap, dtype=np.float32)
+        n = self.lib.oracle_detect_peaks(dp, d.size, int(type_), pos.ctypes.data_as(C.POINTER(C.c_int)),
+                                         val.ctypes.data_as(_fp), cap)
+        return pos[:n].copy(), val[:n].copy()
 
     def overlap_save_length(self, h_length):
         return self.lib.oracle_overlap_save_length(h_length)
@@ -193,6 +205,27 @@ class SimdAPI:
         return (res, info) if return_handle_info else res
 
 
+class ExtremumPoint(C.Structure):
+    # /root/reference/inc/simd/detect_peaks.h:46-49
+    _fields_ = [("position", C.c_int), ("value", C.c_float)]
+
+
+def call_detect_peaks(lib, data, type_=3, simd=0):
+    """detect_peaks through the reference C signature on any library exporting it."""
+    d, dp = _f32(data)
+    lib.detect_peaks.argtypes = [C.c_int, _fp, C.c_size_t, C.c_int,
+                                 C.POINTER(C.POINTER(ExtremumPoint)), C.POINTER(C.c_size_t)]
+    lib.detect_peaks.restype = None
+    res = C.POINTER(ExtremumPoint)()
+    n = C.c_size_t(0)
+    lib.detect_peaks(int(simd), dp, d.size, int(type_), C.byref(res), C.byref(n))
+    pos = np.array([res[i].position for i in range(n.value)], dtype=np.int32)
+    val = np.array([res[i].value for i in range(n.value)], dtype=np.float32)
+    if n.value:
+        C.CDLL(None).free(res)
+    return pos, val
+
+
 class Reference(SimdAPI):
     """The reference's own convolve.c/correlate.c/memory.c compiled against the FFT shim
     (kind == "reference").  Raises FileNotFoundError when oracle/_ref was not built."""
@@ -217,6 +250,9 @@ class Reference(SimdAPI):
                                            out.ctypes.data_as(_fp), out.shape[1], b,
                                            int(reverse), int(algorithm), int(threads))
         return out, used
+
+    def detect_peaks(self, data, type_=3, simd=0):
+        return call_detect_peaks(self.lib, data, type_, simd)
 
     def struct_layout(self):
         arr = (C.c_size_t * 16)()

@@ -354,6 +354,62 @@ def test_real_packed_mode(simd, oracle, monkeypatch):
     monkeypatch.delenv("VELES_B200_REAL")
 
 
+def test_detect_peaks_parity(simd, oracle):
+    """detect_peaks through the C-ABI: bit-exact positions and values against the golden
+    fixtures (reference scalar loop) and the oracle, host and device input, all three types,
+    sizes around tile boundaries, and the device-resident variant."""
+    import os
+    import torch
+    simd.use_torch_stream()
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "peaks.npz"))
+    for name in sorted({k.split("/")[0] for k in z.files}):
+        data = z[name + "/data"]
+        for t in (1, 2, 3):
+            pos, val = simd.detect_peaks(data, t)
+            assert np.array_equal(pos, z[f"{name}/pos{t}"]), (name, t)
+            assert np.array_equal(val, z[f"{name}/val{t}"]), (name, t)
+    rng = np.random.default_rng(8)
+    for n in (3, 4, 2049, 2050, 2051, 4098, 100003, 3_000_001):
+        data = rng.standard_normal(n).astype(np.float32)
+        data[rng.integers(0, n, n // 7)] = 0.0          # plateaus: strict comparisons matter
+        for t in (1, 3):
+            want_p, want_v = oracle.detect_peaks(data, t)
+            got_p, got_v = simd.detect_peaks(data, t)
+            assert np.array_equal(got_p, want_p) and np.array_equal(got_v, want_v), (n, t)
+            dp, dv = simd.detect_peaks(torch.from_numpy(data).cuda(), t)
+            assert np.array_equal(dp, want_p) and np.array_equal(dv, want_v)
+    # device-resident variant, including truncation at capacity
+    data = torch.from_numpy(rng.standard_normal(1_000_000).astype(np.float32)).cuda()
+    want_p, want_v = oracle.detect_peaks(data.cpu().numpy(), 3)
+    out = torch.zeros((want_p.size + 10, 2), dtype=torch.int32, device="cuda")
+    n = simd.detect_peaks_device(data, out, 3)
+    assert n == want_p.size
+    got = out[:n].cpu().numpy()
+    assert np.array_equal(got[:, 0], want_p) and np.array_equal(got[:, 1].copy().view(np.float32), want_v)
+    small = torch.zeros((100, 2), dtype=torch.int32, device="cuda")
+    assert simd.detect_peaks_device(data, small, 3) == want_p.size
+    assert np.array_equal(small.cpu().numpy()[:, 0], want_p[:100])
+
+
+def test_correlate_then_detect_peaks_on_device(simd, oracle):
+    """The consumer chain of SURVEY 8(f): cross-correlate, then pick the extrema of the
+    result without the result ever leaving the GPU."""
+    import torch
+    simd.use_torch_stream()
+    xl, hl = 200000, 300
+    x, h = uni(31, xl), uni(32, hl)
+    xd, hd_ = torch.from_numpy(x).cuda(), torch.from_numpy(h).cuda()
+    with simd.Handle(xl, hl, "", True) as hd:
+        y = hd(xd, hd_)
+        out = torch.zeros((xl + hl, 2), dtype=torch.int32, device="cuda")
+        n = simd.detect_peaks_device(y, out, simd.EXTREMUM_MAXIMUM)
+        torch.cuda.synchronize()
+    yh = y.cpu().numpy()
+    want_p, want_v = oracle.detect_peaks(yh, 1)
+    assert n == want_p.size
+    assert np.array_equal(out[:n, 0].cpu().numpy(), want_p)
+
+
 def test_kernel_launch_counter(simd):
     before = simd.lib.simd_b200_kernel_launches()
     simd.convolve_simd(KAT_X, KAT_H)

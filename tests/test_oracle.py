@@ -126,3 +126,24 @@ def test_oracle_batch_threads(oracle):
     assert used == 2
     for b in range(6):
         assert rel_l2(out[b], oracle.convolve_f64(x[b], h)) < 1e-5
+
+
+def test_detect_peaks_oracle_against_golden_and_reference(oracle, reference_or_none):
+    """SURVEY 8(f) rank 1.  tests/detect_peaks.cc:43-100 known answers + fixtures from the
+    reference's scalar loop; bit-exact (index work)."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "peaks.npz"))
+    names = sorted({k.split("/")[0] for k in z.files})
+    assert {"sin", "nasty", "noise", "corr_c2"} <= set(names)
+    for name in names:
+        data = z[name + "/data"]
+        for t in (1, 2, 3):
+            pos, val = oracle.detect_peaks(data, t)
+            assert np.array_equal(pos, z[f"{name}/pos{t}"]), (name, t)
+            assert np.array_equal(val, z[f"{name}/val{t}"]), (name, t)
+            if reference_or_none is not None:
+                rp, rv = reference_or_none.detect_peaks(data, t, simd=0)
+                assert np.array_equal(pos, rp) and np.array_equal(val, rv)
+    assert z["sin/pos1"].tolist() == [i * 200 + 50 for i in range(20)]
+    assert z["sin/pos2"].tolist() == [i * 200 + 150 for i in range(20)]
+    assert z["nasty/pos1"].tolist() == [7, 16, 97, 99]

@@ -53,6 +53,14 @@ class ConvolutionHandle(C.Structure):
                 ("handle", _HandleUnion)]
 
 
+class ExtremumPoint(C.Structure):
+    """include/simd/detect_peaks.h (reference: detect_peaks.h:46-49)."""
+    _fields_ = [("position", C.c_int), ("value", C.c_float)]
+
+
+EXTREMUM_MAXIMUM, EXTREMUM_MINIMUM, EXTREMUM_BOTH = 1, 2, 3
+
+
 def build(verbose=False):
     """Compile libSimd.so in-tree (nvcc -gencode arch=compute_100a,code=sm_100a)."""
     subprocess.run(["make", "-C", _HERE, "--no-print-directory"] + ([] if verbose else ["-s"]),
@@ -103,6 +111,11 @@ def _load():
     L.simd_b200_profile.restype = None
     L.simd_b200_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
     L.simd_b200_profile_collect.restype = None
+    L.detect_peaks.argtypes = [C.c_int, vp, sz, C.c_int, C.POINTER(C.POINTER(ExtremumPoint)),
+                               C.POINTER(sz)]
+    L.detect_peaks.restype = None
+    L.simd_b200_detect_peaks_device.argtypes = [vp, sz, C.c_int, vp, sz]
+    L.simd_b200_detect_peaks_device.restype = sz
     L.simd_b200_filter_noalloc.argtypes = [vp, sz, vp, sz, C.c_int, vp, vp]
     L.simd_b200_filter_noalloc.restype = C.c_int
     L.mallocf.argtypes = [sz]
@@ -131,7 +144,8 @@ EXPORTED_SYMBOLS = (
     "simd_b200_select_algorithm_batch "
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
-    "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc").split()
+    "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc "
+    "detect_peaks simd_b200_detect_peaks_device").split()
 
 
 def _is_torch(a):
@@ -291,6 +305,27 @@ def convolve(x, h, correlate=False):
 
 def cross_correlate(x, h):
     return convolve(x, h, correlate=True)
+
+
+def detect_peaks(data, type_=EXTREMUM_BOTH, simd=1):
+    """detect_peaks(): (positions int32[], values float32[]) of a host or device series."""
+    if not _is_torch(data):
+        data = np.ascontiguousarray(data, dtype=np.float32)
+    res = C.POINTER(ExtremumPoint)()
+    n = C.c_size_t(0)
+    lib.detect_peaks(int(simd), _ptr(data), data.shape[-1], int(type_), C.byref(res), C.byref(n))
+    if n.value == 0:
+        return np.empty(0, np.int32), np.empty(0, np.float32)
+    raw = np.ctypeslib.as_array(C.cast(res, C.POINTER(C.c_int32)), shape=(n.value, 2)).copy()
+    C.CDLL(None).free(res)
+    return raw[:, 0].copy(), raw[:, 1].copy().view(np.float32)
+
+
+def detect_peaks_device(data, out, type_=EXTREMUM_BOTH):
+    """simd_b200_detect_peaks_device: data, out are CUDA tensors (out: int32 (capacity, 2));
+    returns the number of extrema found (may exceed the capacity)."""
+    return lib.simd_b200_detect_peaks_device(data.data_ptr(), data.numel(), int(type_), out.data_ptr(),
+                                             out.shape[0])
 
 
 def filter_shard(x, h, reverse, left_pad, result_length, algorithm=-1, out=None):

@@ -1,0 +1,223 @@
+// peaks.cu -- detect_peaks on the GPU: ordered stream compaction of local extrema.
+//
+// Replaces /root/reference/src/detect_peaks.c:41-127.  Three launches:
+//   peaks_count_kernel   every CTA classifies a tile of interior points and stores its count
+//   peaks_scan_kernel    one CTA turns the tile counts into exclusive offsets (+ total)
+//   peaks_write_kernel   every CTA re-classifies its tile and writes {position, value} at
+//                        offset[tile] + its in-tile rank, which keeps the list ordered
+// The series is read twice (8 B per sample) and 8 B are written per extremum: HBM-bound.
+#include "b200_device.cuh"
+#include <mutex>
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kPerThread = 8;
+constexpr int kTile = kThreads * kPerThread;
+
+// bit r set <=> interior point i0 + r is an extremum of the requested type
+__device__ __forceinline__ unsigned classify(const float *d, i64 i0, i64 last, int type) {
+  unsigned m = 0;
+  if (i0 > last) return 0;
+  float prev = d[i0 - 1], curr = d[i0];
+#pragma unroll
+  for (int r = 0; r < kPerThread; r++) {
+    const i64 i = i0 + r;
+    if (i > last) break;
+    const float next = d[i + 1];
+    const float d1 = __fsub_rn(curr, prev), d2 = __fsub_rn(curr, next);
+    if (__fmul_rn(d1, d2) > 0.f) {
+      if ((d1 > 0.f && (type & 1)) || (d1 < 0.f && (type & 2))) m |= 1u << r;
+    }
+    prev = curr;
+    curr = next;
+  }
+  return m;
+}
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int *total, int *smem) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  if (lane == 31) smem[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    int w = lane < kThreads / 32 ? smem[lane] : 0;
+    int winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int n = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += n;
+    }
+    smem[32 + lane] = winc - w;           // exclusive warp offsets
+    if (lane == 31) smem[64] = winc;      // block total
+  }
+  __syncthreads();
+  *total = smem[64];
+  return smem[32 + wid] + inc - v;
+}
+
+__global__ void __launch_bounds__(kThreads) peaks_count_kernel(const float *d, i64 size, int type,
+                                                               unsigned *counts) {
+  __shared__ int smem[65];
+  const i64 i0 = 1 + (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
+  const int c = __popc(classify(d, i0, size - 2, type));
+  int total;
+  block_exclusive_scan(c, &total, smem);
+  if (threadIdx.x == 0) counts[blockIdx.x] = (unsigned)total;
+}
+
+// exclusive scan of the `n` tile counts (64-bit running sum); grand total to *total
+__global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts,
+                                                          unsigned long long *offsets, i64 n,
+                                                          unsigned long long *total) {
+  __shared__ unsigned long long warp_off[32];
+  __shared__ unsigned long long chunk_total, carry;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (i64 base = 0; base < n; base += 1024) {
+    const i64 i = base + threadIdx.x;
+    const unsigned long long v = i < n ? counts[i] : 0ull;
+    unsigned long long inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += u;
+    }
+    if (lane == 31) warp_off[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+      const unsigned long long w = warp_off[lane];
+      unsigned long long winc = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long u = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += u;
+      }
+      warp_off[lane] = winc - w;
+      if (lane == 31) chunk_total = winc;
+    }
+    __syncthreads();
+    if (i < n) offsets[i] = carry + warp_off[wid] + inc - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += chunk_total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+__global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i64 size, int type,
+                                                               const unsigned long long *offsets,
+                                                               int2 *out, unsigned long long capacity) {
+  __shared__ int smem[65];
+  const i64 i0 = 1 + (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
+  unsigned m = classify(d, i0, size - 2, type);
+  int total;
+  unsigned long long pos = offsets[blockIdx.x] + (unsigned long long)block_exclusive_scan(__popc(m), &total, smem);
+  while (m) {
+    const int r = __ffs(m) - 1;
+    m &= m - 1;
+    if (pos < capacity) out[pos] = make_int2((int)(i0 + r), __float_as_int(d[i0 + r]));
+    pos++;
+  }
+}
+
+struct PeakScratch {       // grow-only per-device scratch: tile counts, offsets, total
+  unsigned *counts = nullptr;
+  unsigned long long *offsets = nullptr, *total = nullptr;
+  size_t tiles_cap = 0;
+};
+PeakScratch g_peaks[16];
+std::mutex g_peaks_mu;
+
+// returns the number of extrema found; writes at most `capacity` of them (device memory)
+unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_out,
+                             unsigned long long capacity, bool count_only, cudaStream_t stream) {
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev < 16, "device index out of range");
+  const i64 interior = size - 2;
+  const i64 tiles = (interior + kTile - 1) / kTile;
+  B200_REQUIRE(tiles < 2147483647LL && size < 2147483647LL, "series too long for int positions");
+  std::lock_guard<std::mutex> lock(g_peaks_mu);
+  PeakScratch &sc = g_peaks[dev];
+  if ((size_t)tiles > sc.tiles_cap) {
+    if (sc.counts) {
+      B200_CUDA_CHECK(cudaDeviceSynchronize());
+      cudaFree(sc.counts); cudaFree(sc.offsets);
+    }
+    size_t cap = (size_t)tiles + (size_t)tiles / 4 + 64;
+    B200_CUDA_CHECK(cudaMalloc(&sc.counts, sizeof(unsigned) * cap));
+    B200_CUDA_CHECK(cudaMalloc(&sc.offsets, sizeof(unsigned long long) * cap));
+    if (!sc.total) B200_CUDA_CHECK(cudaMalloc(&sc.total, sizeof(unsigned long long)));
+    sc.tiles_cap = cap;
+  }
+  peaks_count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, sc.counts);
+  peaks_scan_kernel<<<1, 1024, 0, stream>>>(sc.counts, sc.offsets, tiles, sc.total);
+  b200_count_launch(2);
+  if (!count_only) {
+    peaks_write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, sc.offsets, d_out,
+                                                                 capacity);
+    b200_count_launch(1);
+  }
+  B200_CUDA_CHECK(cudaGetLastError());
+  unsigned long long total = 0;
+  B200_CUDA_CHECK(cudaMemcpyAsync(&total, sc.total, sizeof(total), cudaMemcpyDeviceToHost, stream));
+  B200_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return total;
+}
+
+bool peaks_is_device_pointer(const void *p) {
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+
+// C-ABI shims used by src/detect_peaks.c -------------------------------------------------------
+
+extern "C" unsigned long long b200_detect_peaks_device(const float *d_data, long long size, int type,
+                                                       void *d_results, unsigned long long capacity) {
+  B200_REQUIRE(d_data && size > 2, "detect_peaks: null data or size <= 2");
+  cudaStream_t stream = (cudaStream_t)b200_get_stream();
+  return peaks_run(d_data, size, type, reinterpret_cast<int2 *>(d_results), capacity,
+                   d_results == nullptr || capacity == 0, stream);
+}
+
+// Host-facing: data may be host or device; *results_host is malloc()ed (NULL when empty).
+extern "C" void b200_detect_peaks(const float *data, long long size, int type, void **results_host,
+                                  size_t *count) {
+  B200_REQUIRE(data && results_host && count, "detect_peaks: null argument");
+  B200_REQUIRE(size > 2, "detect_peaks: size must exceed 2");
+  cudaStream_t stream = (cudaStream_t)b200_get_stream();
+  *results_host = nullptr;
+  *count = 0;
+  const float *d_data = data;
+  float *staged = nullptr;
+  if (!peaks_is_device_pointer(data)) {
+    B200_CUDA_CHECK(cudaMalloc(&staged, sizeof(float) * (size_t)size));
+    B200_CUDA_CHECK(cudaMemcpyAsync(staged, data, sizeof(float) * (size_t)size, cudaMemcpyHostToDevice, stream));
+    d_data = staged;
+  }
+  // pass 1: count; then exact-size output, pass 2: write (the count kernels run again inside)
+  unsigned long long n = peaks_run(d_data, size, type, nullptr, 0, true, stream);
+  if (n > 0) {
+    int2 *d_out = nullptr;
+    B200_CUDA_CHECK(cudaMalloc(&d_out, sizeof(int2) * n));
+    peaks_run(d_data, size, type, d_out, n, false, stream);
+    void *host = malloc(sizeof(int2) * n);
+    B200_REQUIRE(host, "detect_peaks: out of host memory");
+    B200_CUDA_CHECK(cudaMemcpyAsync(host, d_out, sizeof(int2) * n, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA_CHECK(cudaStreamSynchronize(stream));
+    B200_CUDA_CHECK(cudaFree(d_out));
+    *results_host = host;
+    *count = (size_t)n;
+  }
+  if (staged) B200_CUDA_CHECK(cudaFree(staged));
+}
