@@ -219,11 +219,11 @@ def call_detect_peaks(lib, data, type_=3, simd=0):
     res = C.POINTER(ExtremumPoint)()
     n = C.c_size_t(0)
     lib.detect_peaks(int(simd), dp, d.size, int(type_), C.byref(res), C.byref(n))
-    pos = np.array([res[i].position for i in range(n.value)], dtype=np.int32)
-    val = np.array([res[i].value for i in range(n.value)], dtype=np.float32)
-    if n.value:
-        C.CDLL(None).free(res)
-    return pos, val
+    if n.value == 0:
+        return np.empty(0, np.int32), np.empty(0, np.float32)
+    raw = np.ctypeslib.as_array(C.cast(res, C.POINTER(C.c_int32)), shape=(n.value, 2)).copy()
+    C.CDLL(None).free(res)
+    return raw[:, 0].copy(), raw[:, 1].copy().view(np.float32)
 
 
 class Reference(SimdAPI):

@@ -15,22 +15,38 @@ constexpr int kThreads = 256;
 constexpr int kPerThread = 8;
 constexpr int kTile = kThreads * kPerThread;
 
-// bit r set <=> interior point i0 + r is an extremum of the requested type
-__device__ __forceinline__ unsigned classify(const float *d, i64 i0, i64 last, int type) {
+// Thread t of a tile owns the 8 consecutive samples starting at c0 = tile*kTile + t*8 (a
+// multiple of 8, so two aligned 16-byte loads fetch them when the series itself is 16-byte
+// aligned); its left / right neighbours come from the adjacent lanes by shuffle, the warp's
+// two edge lanes load theirs.  Bit r of the result <=> sample c0 + r is an interior point and
+// an extremum of the requested type.  vals[] receives the 8 samples.
+__device__ __forceinline__ unsigned classify(const float *d, i64 c0, i64 size, int type, bool vec,
+                                             float (&vals)[kPerThread]) {
+  const int lane = threadIdx.x & 31;
+  if (vec && c0 + kPerThread <= size) {
+    const float4 a = *reinterpret_cast<const float4 *>(d + c0);
+    const float4 b = *reinterpret_cast<const float4 *>(d + c0 + 4);
+    vals[0] = a.x; vals[1] = a.y; vals[2] = a.z; vals[3] = a.w;
+    vals[4] = b.x; vals[5] = b.y; vals[6] = b.z; vals[7] = b.w;
+  } else {
+#pragma unroll
+    for (int r = 0; r < kPerThread; r++) vals[r] = c0 + r < size ? d[c0 + r] : 0.f;
+  }
+  float left = __shfl_up_sync(0xffffffffu, vals[kPerThread - 1], 1);
+  float right = __shfl_down_sync(0xffffffffu, vals[0], 1);
+  if (lane == 0) left = c0 > 0 && c0 - 1 < size ? d[c0 - 1] : 0.f;
+  if (lane == 31) right = c0 + kPerThread < size ? d[c0 + kPerThread] : 0.f;
   unsigned m = 0;
-  if (i0 > last) return 0;
-  float prev = d[i0 - 1], curr = d[i0];
 #pragma unroll
   for (int r = 0; r < kPerThread; r++) {
-    const i64 i = i0 + r;
-    if (i > last) break;
-    const float next = d[i + 1];
-    const float d1 = __fsub_rn(curr, prev), d2 = __fsub_rn(curr, next);
-    if (__fmul_rn(d1, d2) > 0.f) {
+    const i64 i = c0 + r;
+    const float prev = r == 0 ? left : vals[r - 1];
+    const float next = r == kPerThread - 1 ? right : vals[r + 1];
+    const float d1 = __fsub_rn(vals[r], prev), d2 = __fsub_rn(vals[r], next);
+    const bool interior = i >= 1 && i <= size - 2;
+    if (interior && __fmul_rn(d1, d2) > 0.f) {
       if ((d1 > 0.f && (type & 1)) || (d1 < 0.f && (type & 2))) m |= 1u << r;
     }
-    prev = curr;
-    curr = next;
   }
   return m;
 }
@@ -62,10 +78,11 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *total, int *smem
 }
 
 __global__ void __launch_bounds__(kThreads) peaks_count_kernel(const float *d, i64 size, int type,
-                                                               unsigned *counts) {
+                                                               bool vec, unsigned *counts) {
   __shared__ int smem[65];
-  const i64 i0 = 1 + (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
-  const int c = __popc(classify(d, i0, size - 2, type));
+  const i64 c0 = (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
+  float vals[kPerThread];
+  const int c = __popc(classify(d, c0, size, type, vec, vals));
   int total;
   block_exclusive_scan(c, &total, smem);
   if (threadIdx.x == 0) counts[blockIdx.x] = (unsigned)total;
@@ -112,18 +129,25 @@ __global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts
 }
 
 __global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i64 size, int type,
+                                                               bool vec,
                                                                const unsigned long long *offsets,
                                                                int2 *out, unsigned long long capacity) {
   __shared__ int smem[65];
-  const i64 i0 = 1 + (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
-  unsigned m = classify(d, i0, size - 2, type);
+  __shared__ int2 staged[kTile];          // the tile's points in rank order
+  const i64 c0 = (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
+  float vals[kPerThread];
+  unsigned m = classify(d, c0, size, type, vec, vals);
   int total;
-  unsigned long long pos = offsets[blockIdx.x] + (unsigned long long)block_exclusive_scan(__popc(m), &total, smem);
-  while (m) {
-    const int r = __ffs(m) - 1;
-    m &= m - 1;
-    if (pos < capacity) out[pos] = make_int2((int)(i0 + r), __float_as_int(d[i0 + r]));
-    pos++;
+  int rank = block_exclusive_scan(__popc(m), &total, smem);
+#pragma unroll
+  for (int r = 0; r < kPerThread; r++) {
+    if (m & (1u << r)) staged[rank++] = make_int2((int)(c0 + r), __float_as_int(vals[r]));
+  }
+  __syncthreads();
+  // coalesced copy of the compacted tile to its place in the global list
+  const unsigned long long base = offsets[blockIdx.x];
+  for (int k = threadIdx.x; k < total; k += kThreads) {
+    if (base + k < capacity) out[base + k] = staged[k];
   }
 }
 
@@ -141,8 +165,8 @@ unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_ou
   int dev = 0;
   B200_CUDA_CHECK(cudaGetDevice(&dev));
   B200_REQUIRE(dev < 16, "device index out of range");
-  const i64 interior = size - 2;
-  const i64 tiles = (interior + kTile - 1) / kTile;
+  const i64 tiles = (size + kTile - 1) / kTile;
+  const bool vec = (((unsigned long long)d_data) & 15ull) == 0;
   B200_REQUIRE(tiles < 2147483647LL && size < 2147483647LL, "series too long for int positions");
   std::lock_guard<std::mutex> lock(g_peaks_mu);
   PeakScratch &sc = g_peaks[dev];
@@ -157,12 +181,12 @@ unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_ou
     if (!sc.total) B200_CUDA_CHECK(cudaMalloc(&sc.total, sizeof(unsigned long long)));
     sc.tiles_cap = cap;
   }
-  peaks_count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, sc.counts);
+  peaks_count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, vec, sc.counts);
   peaks_scan_kernel<<<1, 1024, 0, stream>>>(sc.counts, sc.offsets, tiles, sc.total);
   b200_count_launch(2);
   if (!count_only) {
-    peaks_write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, sc.offsets, d_out,
-                                                                 capacity);
+    peaks_write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, vec, sc.offsets,
+                                                                 d_out, capacity);
     b200_count_launch(1);
   }
   B200_CUDA_CHECK(cudaGetLastError());
