@@ -50,6 +50,17 @@ namespace fc {
 
 typedef long long i64;
 
+// Before the first pass of a pair overwrites the transform buffer: the bulk store that is
+// still reading the previous pair's staged results out of it must have finished reading.
+FC_HD void wait_staged_results_read(int t) {
+#if defined(__CUDA_ARCH__)
+  if (t == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  __syncthreads();
+#else
+  (void)t;
+#endif
+}
+
 template <int I, int END, class F>
 FC_HD void static_for(F &&f) {
   if constexpr (I < END) {
@@ -339,7 +350,7 @@ FC_HD void fwd_first(int t, const SegPair &w, const TwBases<P> &tb, float2 *sm) 
 // `step` samples later, so its head does too and only its tail is read from global memory.
 template <class P>
 FC_HD void fwd_first_parked(int t, const SegPair &w, const TwBases<P> &tb, float2 *sm,
-                            const float *park, int park_len, int step) {
+                            const float *park, int park_len, int step, bool wait_store) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
   static_for<0, P::E / R>([&](auto jj) {
@@ -368,6 +379,8 @@ FC_HD void fwd_first_parked(int t, const SegPair &w, const TwBases<P> &tb, float
         v[k] = cmul(v[k], pw.template get<k>());
       });
     }
+    static_assert(P::E / R == 1, "persistent kernel: one first-pass butterfly per thread");
+    if (wait_store) wait_staged_results_read(t);      // CTA-uniform
     static_for<0, R>([&](auto kk) {
       constexpr int k = decltype(kk)::value;
       smb[G::off(k)] = v[k];
@@ -534,6 +547,80 @@ FC_HD void inv_last(int t, const SegPair &w, const TwBases<P> &tb, const float2 
         if (tt < (unsigned)w.cntB) ob[r * G::S] = w.accumulate ? ob[r * G::S] + v[r].y : v[r].y;
       });
     }
+  });
+}
+
+// inverse last pass without the global stores: natural-order circular samples stay in v[]
+// (register j*R + r holds circular index base_j + r*S; .x -> segment A, .y -> segment B).
+template <class P>
+FC_HD void inv_last_regs(int t, const TwBases<P> &tb, const float2 *sm, float2 *v) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    auto *smb = sm + pad_pos(base);
+    float2 *vj = v + j * R;
+    if constexpr (G::S > 1) {
+      Powers<R> pw;
+      pw.init(tb.w1[j]);
+      static_for<0, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        float2 e = smb[G::off(k)];
+        if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
+        vj[bitrev(k, ilog2(R))] = e;
+      });
+    } else {
+      static_for<0, R>([&](auto kk) {
+        constexpr int k = decltype(kk)::value;
+        vj[bitrev(k, ilog2(R))] = smb[G::off(k)];
+      });
+    }
+    dft_inreg<R, true>(vj);
+  });
+}
+
+// Results of a full segment pair into a shared-memory staging area (two float arrays, the
+// element for output index tt at stage[phase + tt]) from where a bulk copy takes them to HBM.
+template <class P>
+FC_HD void stage_outputs(int t, const float2 *v, int c_off, int step, int phase, float *stA,
+                         float *stB) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const unsigned tt = (unsigned)(base + r * G::S - c_off);      // negative -> huge
+      if (tt < (unsigned)step) {
+        stA[phase + tt] = v[j * R + r].x;
+        stB[phase + tt] = v[j * R + r].y;
+      }
+    });
+  });
+}
+
+// Guarded direct stores of the same register contents (edge pairs, accumulation).
+template <class P>
+FC_HD void store_outputs(int t, const SegPair &w, const float2 *v) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, npp, bf;
+    G::locate(t, j, base, npp, bf);
+    const int t0 = base - w.c_off;
+    float *oa = w.out + (w.outA + t0);
+    float *ob = w.out + (w.outB + t0);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const unsigned tt = (unsigned)(t0 + r * G::S);
+      if (tt < (unsigned)w.cntA) oa[r * G::S] = w.accumulate ? oa[r * G::S] + v[j * R + r].x : v[j * R + r].x;
+      if (tt < (unsigned)w.cntB) ob[r * G::S] = w.accumulate ? ob[r * G::S] + v[j * R + r].y : v[j * R + r].y;
+    });
   });
 }
 

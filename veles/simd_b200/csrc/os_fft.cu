@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
     if (parked && t == 0) issue_park(w0);
   }
   unsigned parity = 0;
+  bool store_pending = false;     // a bulk store is still reading staged results from `sm`
   asm volatile("griddepcontrol.wait;" ::: "memory");     // the spectrum kernel is short
   for (; item < p.total; item += gridDim.x) {
     {
@@ -360,10 +361,12 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
       if (parked) {
         mbar_wait(bar, parity);
         parity ^= 1u;
-        fwd_first_parked<P>(t, w, tb, sm, park, park_len, p.step);
+        fwd_first_parked<P>(t, w, tb, sm, park, park_len, p.step, store_pending);
       } else {
+        if (store_pending) wait_staged_results_read(t);
         fwd_first<P>(t, w, tb, sm);
       }
+      store_pending = false;
     }
     __syncthreads();            // first-pass results visible; the parked range is consumed
     // start fetching the next pair's input while this pair is transformed
@@ -392,11 +395,46 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
     {
       SegPair w;
       pair_of(item, w);
-      const TwBases<P> tb = tb_sm[t];
-      inv_last<P>(t, w, tb, sm);
+      float2 v[P::E];
+      { const TwBases<P> tb = tb_sm[t]; inv_last_regs<P>(t, tb, sm, v); }
+      const bool full = !w.accumulate && w.haveB && w.cntA == p.step && w.cntB == p.step;
+      if (full) {
+        // Results leave through shared memory and one bulk copy per segment (TMA store): the
+        // warps do not wait for the stores to drain, the next pair's first pass computes
+        // meanwhile.  stage[phase + tt] keeps shared and global addresses congruent mod 16 B.
+        float *st = reinterpret_cast<float *>(sm);
+        const int phase = (int)((((unsigned long long)(w.out + w.outA)) >> 2) & 3ull);
+        const int span = (p.step + 8 + 3) & ~3;
+        float *stA = st, *stB = st + span;
+        __syncthreads();                  // every thread has read its last-pass inputs
+        stage_outputs<P>(t, v, w.c_off, p.step, phase, stA, stB);
+        __syncthreads();
+        const int head = (4 - phase) & 3;
+        const int mid = (p.step - head) & ~3;
+        const int tail = p.step - head - mid;
+        float *ga = w.out + w.outA, *gb = w.out + w.outB;
+        if (t < head) { ga[t] = stA[phase + t]; gb[t] = stB[phase + t]; }
+        if (t >= 32 && t < 32 + tail) {
+          const int k = head + mid + (t - 32);
+          ga[k] = stA[phase + k]; gb[k] = stB[phase + k];
+        }
+        if (t == 0) {
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          const unsigned bytes = (unsigned)mid * 4u;
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(ga + head),
+                       "r"(smem_u32(stA + phase + head)), "r"(bytes) : "memory");
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gb + head),
+                       "r"(smem_u32(stB + phase + head)), "r"(bytes) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        store_pending = true;
+      } else {
+        store_outputs<P>(t, w, v);
+      }
     }
-    // the next first pass writes only positions this thread has just read: no barrier here
   }
+  // staged results must be out of shared memory before the CTA retires
+  if (t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // ---- plan table ---------------------------------------------------------------------------
