@@ -317,13 +317,22 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
   const bool slice_time = job->batch == 1 && o_row > budget;
   i64 rows_per_piece = 1, outs_per_piece = o_row;
   if (slice_time) {
-    outs_per_piece = budget / 2;
+    outs_per_piece = budget / 4;                            // 16 MiB slices of one long signal
   } else {
     rows_per_piece = budget / (x_row > o_row ? x_row : o_row);
     if (rows_per_piece < 1) rows_per_piece = 1;
     if (rows_per_piece > job->batch) rows_per_piece = job->batch;
-    // at least ~8 pieces when the batch allows, so the pipeline has something to overlap
-    if (job->batch >= 16 && rows_per_piece > job->batch / 8) rows_per_piece = job->batch / 8;
+    // Aim for ~32 pieces of at least ~8 MiB: the pipeline's fill (first H2D) and drain (last
+    // D2H) are not overlapped, so they should be a small fraction of the whole.
+    {
+      const i64 row_floats = x_row > o_row ? x_row : o_row;
+      i64 min_rows = ((i64)2 << 20) / row_floats;           // >= 8 MiB per piece
+      if (min_rows < 1) min_rows = 1;
+      i64 want = job->batch / 32;
+      if (want < min_rows) want = min_rows;
+      if (rows_per_piece > want) rows_per_piece = want;
+      if (rows_per_piece < 1) rows_per_piece = 1;
+    }
   }
   const i64 piece_x = slice_time ? outs_per_piece + job->h_len : rows_per_piece * x_row;
   const i64 piece_o = slice_time ? outs_per_piece : rows_per_piece * o_row;
