@@ -23,3 +23,17 @@ size_t oracle_detect_peaks(const float *data, size_t size, int type, int *positi
   }
   return n;
 }
+
+/* minmax1D, scalar path: /root/reference/src/normalize.c:425-443 (minmax1D_novec).  Pinned
+ * against the reference's test (tests/normalize.cc:65-81) and oracle/_ref (bit-exact). */
+__attribute__((visibility("default")))
+void oracle_minmax1D(const float *src, int length, float *min_out, float *max_out) {
+  float mn = src[0], mx = src[0];
+  for (int i = 0; i < length; i++) {
+    float val = src[i];
+    if (val < mn) mn = val;
+    if (val > mx) mx = val;
+  }
+  if (min_out) *min_out = mn;
+  if (max_out) *max_out = mx;
+}

@@ -50,6 +50,8 @@ class Oracle:
         L.oracle_convolve_batch.restype = C.c_int
         L.oracle_detect_peaks.argtypes = [_fp, sz, C.c_int, C.POINTER(C.c_int), _fp, sz]
         L.oracle_detect_peaks.restype = sz
+        L.oracle_minmax1D.argtypes = [_fp, C.c_int, _fp, _fp]
+        L.oracle_minmax1D.restype = None
 
     def _run(self, fn, x, h, *extra):
         x, xp = _f32(x)
@@ -92,6 +94,12 @@ class Oracle:
         n = self.lib.oracle_detect_peaks(dp, d.size, int(type_), pos.ctypes.data_as(C.POINTER(C.c_int)),
                                          val.ctypes.data_as(_fp), cap)
         return pos[:n].copy(), val[:n].copy()
+
+    def minmax1D(self, data):
+        d, dp = _f32(data)
+        mn, mx = C.c_float(), C.c_float()
+        self.lib.oracle_minmax1D(dp, d.size, C.byref(mn), C.byref(mx))
+        return mn.value, mx.value
 
     def overlap_save_length(self, h_length):
         return self.lib.oracle_overlap_save_length(h_length)
@@ -253,6 +261,14 @@ class Reference(SimdAPI):
 
     def detect_peaks(self, data, type_=3, simd=0):
         return call_detect_peaks(self.lib, data, type_, simd)
+
+    def minmax1D(self, data, simd=1):
+        d, dp = _f32(data)
+        self.lib.minmax1D.argtypes = [C.c_int, _fp, C.c_int, _fp, _fp]
+        self.lib.minmax1D.restype = None
+        mn, mx = C.c_float(), C.c_float()
+        self.lib.minmax1D(int(simd), dp, d.size, C.byref(mn), C.byref(mx))
+        return mn.value, mx.value
 
     def struct_layout(self):
         arr = (C.c_size_t * 16)()

@@ -410,6 +410,33 @@ def test_correlate_then_detect_peaks_on_device(simd, oracle):
     assert np.array_equal(out[:n, 0].cpu().numpy(), want_p)
 
 
+def test_minmax1D_parity(simd, oracle):
+    """minmax1D through the C-ABI: bit-exact (min / max are exact) for host and device input,
+    lengths around the vector / tile boundaries, NULL result pointers."""
+    import ctypes as C
+    import torch
+    simd.use_torch_stream()
+    a = np.ones(100, np.float32)
+    a[[0, 1, 10, 89, 21]] = [127, 15, 252, 31, 3]          # tests/normalize.cc:65-81
+    assert simd.minmax1D(a) == (1.0, 252.0)
+    mx = C.c_float()
+    simd.lib.minmax1D(1, a.ctypes.data, 100, None, C.byref(mx))
+    assert mx.value == 252.0
+    simd.lib.minmax1D(1, a.ctypes.data, 100, None, None)
+    rng = np.random.default_rng(6)
+    for n in (1, 2, 3, 5, 1023, 1024, 1025, 300001, 5_000_003):
+        x = rng.standard_normal(n).astype(np.float32)
+        want = oracle.minmax1D(x)
+        assert simd.minmax1D(x) == want
+        assert simd.minmax1D(x[1:]) == oracle.minmax1D(x[1:]) if n > 1 else True   # misaligned
+        xd = torch.from_numpy(x).cuda()
+        assert simd.minmax1D(xd) == want
+        out = torch.zeros(2, device="cuda")
+        simd.lib.simd_b200_minmax1D_device(xd.data_ptr(), n, out.data_ptr())
+        torch.cuda.synchronize()
+        assert tuple(out.cpu().tolist()) == want
+
+
 def test_kernel_launch_counter(simd):
     before = simd.lib.simd_b200_kernel_launches()
     simd.convolve_simd(KAT_X, KAT_H)

@@ -147,3 +147,17 @@ def test_detect_peaks_oracle_against_golden_and_reference(oracle, reference_or_n
     assert z["sin/pos1"].tolist() == [i * 200 + 50 for i in range(20)]
     assert z["sin/pos2"].tolist() == [i * 200 + 150 for i in range(20)]
     assert z["nasty/pos1"].tolist() == [7, 16, 97, 99]
+
+
+def test_minmax1D_oracle(oracle, reference_or_none):
+    """SURVEY 8(f) rank 3.  tests/normalize.cc:65-81 known answer + the reference build."""
+    a = np.ones(100, np.float32)
+    a[[0, 1, 10, 89, 21]] = [127, 15, 252, 31, 3]
+    assert oracle.minmax1D(a) == (1.0, 252.0)
+    rng = np.random.default_rng(4)
+    for n in (1, 7, 8, 9, 1000, 100003):
+        x = rng.standard_normal(n).astype(np.float32)
+        assert oracle.minmax1D(x) == (float(x.min()), float(x.max()))
+        if reference_or_none is not None:
+            assert reference_or_none.minmax1D(x, 1) == oracle.minmax1D(x)
+            assert reference_or_none.minmax1D(x, 0) == oracle.minmax1D(x)

@@ -116,6 +116,10 @@ def _load():
     L.detect_peaks.restype = None
     L.simd_b200_detect_peaks_device.argtypes = [vp, sz, C.c_int, vp, sz]
     L.simd_b200_detect_peaks_device.restype = sz
+    L.minmax1D.argtypes = [C.c_int, vp, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.minmax1D.restype = None
+    L.simd_b200_minmax1D_device.argtypes = [vp, sz, vp]
+    L.simd_b200_minmax1D_device.restype = None
     L.simd_b200_filter_noalloc.argtypes = [vp, sz, vp, sz, C.c_int, vp, vp]
     L.simd_b200_filter_noalloc.restype = C.c_int
     L.mallocf.argtypes = [sz]
@@ -145,7 +149,7 @@ EXPORTED_SYMBOLS = (
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
     "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc "
-    "detect_peaks simd_b200_detect_peaks_device").split()
+    "detect_peaks simd_b200_detect_peaks_device minmax1D simd_b200_minmax1D_device").split()
 
 
 def _is_torch(a):
@@ -305,6 +309,15 @@ def convolve(x, h, correlate=False):
 
 def cross_correlate(x, h):
     return convolve(x, h, correlate=True)
+
+
+def minmax1D(data, simd=1):
+    """minmax1D(): (min, max) of a host or device series."""
+    if not _is_torch(data):
+        data = np.ascontiguousarray(data, dtype=np.float32)
+    mn, mx = C.c_float(), C.c_float()
+    lib.minmax1D(int(simd), _ptr(data), data.shape[-1], C.byref(mn), C.byref(mx))
+    return mn.value, mx.value
 
 
 def detect_peaks(data, type_=EXTREMUM_BOTH, simd=1):
