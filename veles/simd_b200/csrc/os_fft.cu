@@ -56,6 +56,33 @@ struct SpecParams {
   float scale;
 };
 
+// Barrier over the threads that share one transform.  Transforms of up to 32 threads live
+// inside a warp (warp-level barrier: groups in one CTA never wait for each other); larger
+// groups of a multi-group CTA use a named barrier of their own; a single group is the CTA.
+template <class P, int G>
+__device__ __forceinline__ void group_sync(int grp) {
+  if constexpr (P::T <= 32) {
+    __syncwarp();
+  } else if constexpr (G > 1) {
+    asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "n"(P::T) : "memory");
+  } else {
+    __syncthreads();
+  }
+}
+
+// item -> (signal, unit inside the signal); 32-bit division when the numbers allow it (the
+// 64-bit one costs more than a radix-4 butterfly network on the small plans)
+__device__ __forceinline__ void split_item(i64 item, i64 per_signal, i64 &sig, i64 &unit) {
+  if (((item | per_signal) >> 31) == 0) {
+    const unsigned q = (unsigned)item / (unsigned)per_signal;
+    sig = q;
+    unit = (unsigned)item - q * (unsigned)per_signal;
+  } else {
+    sig = item / per_signal;
+    unit = item - sig * per_signal;
+  }
+}
+
 template <class P>
 __global__ void __launch_bounds__(P::T) os_spectrum_kernel(SpecParams p) {
   extern __shared__ float4 smem4[];
@@ -102,8 +129,9 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     // computes (CTAs are dispatched in index order, one wave = p.prefetch_distance items).
     const i64 nxt = item + p.prefetch_distance;
     if (p.prefetch_distance > 0 && nxt < p.total) {
-      const i64 nb = nxt / p.npairs;
-      const i64 nsa = (nxt % p.npairs) * 2;
+      i64 nb, nsa;
+      split_item(nxt, p.npairs, nb, nsa);
+      nsa *= 2;
       i64 lo = nsa * p.step + p.in_shift;
       i64 hi = lo + p.step + P::N;
       if (lo < 0) lo = 0;
@@ -119,8 +147,9 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
   }
   if (live) {
     load_twiddle_bases<P>(t, p.tw, tb);
-    const i64 b = item / p.npairs;
-    const i64 sa = (item % p.npairs) * 2;
+    i64 b, sa;
+    split_item(item, p.npairs, b, sa);
+    sa *= 2;
     w.x = p.x + b * p.x_stride;
     w.x_len = p.x_len;
     w.inA = sa * p.step + p.in_shift;
@@ -136,7 +165,7 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     w.accumulate = p.accumulate != 0;
     fwd_first<P>(t, w, tb, sm);
   }
-  __syncthreads();
+  group_sync<P, G>(grp);
   if constexpr (P::NPASS == 3) {
     // Between the first and the last pass every half-warp works on sub-blocks nobody else
     // touches (PassGeom::locate_mid / locate_centre), so warp-level barriers suffice and the
@@ -155,7 +184,7 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
     if (live) load_spectrum<P>(t, p.spectrum, hr);
     if (live) centre<P>(t, hr, sm);
   }
-  __syncthreads();
+  group_sync<P, G>(grp);
   if (live) inv_last<P>(t, w, tb, sm);
 }
 
@@ -198,8 +227,9 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
   if (t == 0) {
     const i64 nxt = item + p.prefetch_distance;
     if (p.prefetch_distance > 0 && nxt < p.total) {
-      const i64 nb = nxt / p.nseg;
-      i64 lo = (nxt % p.nseg) * p.step + p.in_shift;
+      i64 nb, nsg;
+      split_item(nxt, p.nseg, nb, nsg);
+      i64 lo = nsg * p.step + p.in_shift;
       i64 hi = lo + 2 * P::N;
       if (lo < 0) lo = 0;
       if (hi > p.x_len) hi = p.x_len;
@@ -214,8 +244,8 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
   }
   if (live) {
     load_twiddle_bases<P>(t, p.tw, tb);
-    const i64 b = item / p.nseg;
-    const i64 sg = item % p.nseg;
+    i64 b, sg;
+    split_item(item, p.nseg, b, sg);
     w.x = p.x + b * p.x_stride;
     w.x_len = p.x_len;
     w.in0 = sg * p.step + p.in_shift;
@@ -227,22 +257,22 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
     w.accumulate = p.accumulate != 0;
     fwd_first_real<P>(t, w, tb, sm);
   }
-  __syncthreads();
+  group_sync<P, G>(grp);
   if constexpr (P::NPASS == 3) {
     if (live) fwd_mid<P>(t, tb, sm);
     __syncwarp();                       // middle passes stay inside the half-warp
   }
   if (live) centre_real_fwd<P>(t, sm);
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  __syncthreads();                      // mirror bins live in other warps
+  group_sync<P, G>(grp);                // mirror bins live in other threads of the group
   if (live) centre_real_mix<P>(t, reinterpret_cast<const float4 *>(p.spectrum), sm, u);
-  __syncthreads();                      // every mirror has been read: safe to overwrite
+  group_sync<P, G>(grp);                // every mirror has been read: safe to overwrite
   if (live) centre_real_store<P>(t, sm, u);
   if constexpr (P::NPASS == 3) {
     __syncwarp();
     if (live) inv_mid<P>(t, tb, sm);
   }
-  __syncthreads();
+  group_sync<P, G>(grp);
   if (live) inv_last_real<P>(t, w, tb, sm);
 }
 

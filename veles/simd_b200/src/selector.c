@@ -23,8 +23,8 @@
  * c(N) is not monotone in N: transforms up to 2048 points run many CTAs per SM and overlap
  * shared-memory traffic with arithmetic, the 8192/16384-point plans run 2 / 1 CTA per SM. */
 static const struct { int n; double c; } kFusedCost[] = {
-  {256, 118.0}, {512, 147.0}, {1024, 145.0}, {2048, 147.0}, {4096, 196.0}, {8192, 210.0},
-  {16384, 255.0},
+  {256, 111.0}, {512, 147.0}, {1024, 150.0}, {2048, 149.0}, {4096, 192.0}, {8192, 203.0},
+  {16384, 237.0},
 };
 #define B200_DIRECT_US_PER_MAC 4.5e-8
 #define B200_DIRECT_LAUNCH_US 9.0
