@@ -110,7 +110,8 @@ def test_selector_is_pure_host_logic(simd):
         assert 256 <= n <= 16384 and n & (n - 1) == 0
     assert simd.transform_length(5000, 3000) == 8192      # whole signal: next pow2 >= x+h-1
     assert simd.transform_length(262144, 4096) == 16384
-    assert simd.transform_length(1 << 20, 64) == 2048
+    assert simd.transform_length(1 << 20, 64) == 256       # two-pass plan, 8 transforms per CTA
+    assert simd.transform_length(1 << 20, 300) == 2048
 
 
 def test_memory_helpers(simd):
