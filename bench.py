@@ -42,6 +42,7 @@ WORKLOADS = {
     "c5": ("convolve", 1, 2 ** 30, 8192, "single long signal x=2^30, h=8192"),
     # SURVEY 8(f) rank 1 (not a BASELINE config): extrema of a 2^28-sample series
     "peaks": ("detect_peaks", 1, 2 ** 28, 0, "detect_peaks (both kinds) on 2^28 uniform random samples"),
+    "minmax": ("minmax1D", 1, 2 ** 28, 0, "minmax1D on 2^28 uniform random samples"),
 }
 FP32_PEAK_TFLOPS = 72.1   # measured on this pool's B200 (tools/ffma_peak, profiles/ffma_peak_r01.json)
 
@@ -233,6 +234,8 @@ def main():
         return run_sharded_long_signal(args, v, world, rank, local)
     if args.workload == "peaks":
         return run_detect_peaks(args, v, world, rank)
+    if args.workload == "minmax":
+        return run_minmax(args, v, world, rank)
     g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
     x = torch.rand((batch, x_len), generator=g, device="cuda") * 2 - 1
     h = torch.rand((h_len,), generator=g, device="cuda") * 2 - 1
@@ -500,6 +503,57 @@ def run_detect_peaks(args, v, world, rank):
                          "frac": ach / peaks["hbm_gbs"], "traffic": None,
                          "kernel": "peaks_count + peaks_scan + peaks_write (whole call)",
                          "algorithmic_bytes_per_launch": abytes},
+            "cpu_baseline": base, "clocks": None}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def run_minmax(args, v, world, rank):
+    """minmax1D, device-resident: algorithmic bytes = 4 per sample (read once)."""
+    import numpy as np
+    import torch
+    _, _, size, _, desc = WORKLOADS["minmax"]
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
+    data = torch.rand((size,), generator=g, device="cuda") * 2 - 1
+    out = torch.zeros(2, device="cuda")
+    call = lambda: v.lib.simd_b200_minmax1D_device(data.data_ptr(), size, out.data_ptr())
+    for _ in range(args.warmup):
+        call()
+    torch.cuda.synchronize()
+    launches0 = v.lib.simd_b200_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    assert tuple(out.cpu().tolist()) == (float(data.min()), float(data.max()))
+    peaks, _ = load_peaks()
+    ach = 4.0 * size / (ms * 1e-3) / 1e9
+    base = None
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from _oracle import Oracle, Reference, have_reference
+        sample = np.random.default_rng(1).uniform(-1, 1, 2 ** 24).astype(np.float32)
+        impl, kind = (Reference(), "reference") if have_reference() else (Oracle(), "port")
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 2.0:
+            impl.minmax1D(sample)
+            reps += 1
+        dt = time.perf_counter() - t0
+        base = {"value": reps * sample.size / dt / 1e9, "unit": "GSamples/s", "cores": 1, "kind": kind,
+                "sample": f"2^24 samples, {reps} repetitions in {dt:.2f} s, single thread (AVX path)"}
+    line = {"metric": "minmax1d_input_gsamples_per_s", "value": size / (ms * 1e-3) / 1e9,
+            "unit": "GSamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": f"minmax: {desc}",
+                                                             "l2": "inputs larger than L2"},
+            "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0), "e2e": None,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": ach / peaks["hbm_gbs"], "traffic": None,
+                         "kernel": "minmax_partial_kernel (+ one-CTA final)",
+                         "algorithmic_bytes_per_launch": 4.0 * size},
             "cpu_baseline": base, "clocks": None}
     if rank == 0:
         print(json.dumps(line), flush=True)

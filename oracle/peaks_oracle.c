@@ -37,3 +37,24 @@ void oracle_minmax1D(const float *src, int length, float *min_out, float *max_ou
   if (min_out) *min_out = mn;
   if (max_out) *max_out = mx;
 }
+
+/* int16 <-> float converters, scalar semantics of /root/reference/inc/simd/arithmetic.h:43-57
+ * (int16_to_float_na, float_to_int16_na: plain casts, truncation toward zero).  Out-of-range
+ * floats saturate as the reference's AVX pack does (:250-278); the scalar cast is undefined
+ * there, so parity tests stay in range.  Pinned bit-exact against the reference's own inline
+ * functions called through oracle/_ref (ref_harness.c). */
+#include <stdint.h>
+__attribute__((visibility("default")))
+void oracle_int16_to_float(const int16_t *data, size_t length, float *res) {
+  for (size_t i = 0; i < length; i++) res[i] = (float)data[i];
+}
+__attribute__((visibility("default")))
+void oracle_float_to_int16(const float *data, size_t length, int16_t *res) {
+  for (size_t i = 0; i < length; i++) {
+    float v = data[i];
+    if (v != v) { res[i] = 0; continue; }
+    if (v >= 32767.f) { res[i] = 32767; continue; }
+    if (v <= -32768.f) { res[i] = -32768; continue; }
+    res[i] = (int16_t)v;
+  }
+}

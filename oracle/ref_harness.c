@@ -82,3 +82,13 @@ REF_API void ref_struct_layout(size_t out[16]) {
   out[14] = offsetof(ConvolutionHandle, x_length);
   out[15] = offsetof(ConvolutionHandle, handle);
 }
+
+/* the reference's converters are header inlines (inc/simd/arithmetic.h): export callable
+ * copies of its scalar versions for the oracle tests */
+#include <simd/arithmetic.h>
+REF_API void ref_int16_to_float_na(const int16_t *data, size_t length, float *res) {
+  int16_to_float_na(data, length, res);
+}
+REF_API void ref_float_to_int16_na(const float *data, size_t length, int16_t *res) {
+  float_to_int16_na(data, length, res);
+}

@@ -52,6 +52,8 @@ class Oracle:
         L.oracle_detect_peaks.restype = sz
         L.oracle_minmax1D.argtypes = [_fp, C.c_int, _fp, _fp]
         L.oracle_minmax1D.restype = None
+        L.oracle_int16_to_float.argtypes = [C.c_void_p, sz, _fp]
+        L.oracle_float_to_int16.argtypes = [_fp, sz, C.c_void_p]
 
     def _run(self, fn, x, h, *extra):
         x, xp = _f32(x)
@@ -94,6 +96,18 @@ class Oracle:
         n = self.lib.oracle_detect_peaks(dp, d.size, int(type_), pos.ctypes.data_as(C.POINTER(C.c_int)),
                                          val.ctypes.data_as(_fp), cap)
         return pos[:n].copy(), val[:n].copy()
+
+    def int16_to_float(self, data):
+        d = np.ascontiguousarray(data, dtype=np.int16)
+        out = np.empty(d.size, dtype=np.float32)
+        self.lib.oracle_int16_to_float(d.ctypes.data, d.size, out.ctypes.data_as(_fp))
+        return out
+
+    def float_to_int16(self, data):
+        d, dp = _f32(data)
+        out = np.empty(d.size, dtype=np.int16)
+        self.lib.oracle_float_to_int16(dp, d.size, out.ctypes.data)
+        return out
 
     def minmax1D(self, data):
         d, dp = _f32(data)
@@ -261,6 +275,20 @@ class Reference(SimdAPI):
 
     def detect_peaks(self, data, type_=3, simd=0):
         return call_detect_peaks(self.lib, data, type_, simd)
+
+    def int16_to_float(self, data):
+        d = np.ascontiguousarray(data, dtype=np.int16)
+        out = np.empty(d.size, dtype=np.float32)
+        self.lib.ref_int16_to_float_na.argtypes = [C.c_void_p, C.c_size_t, _fp]
+        self.lib.ref_int16_to_float_na(d.ctypes.data, d.size, out.ctypes.data_as(_fp))
+        return out
+
+    def float_to_int16(self, data):
+        d, dp = _f32(data)
+        out = np.empty(d.size, dtype=np.int16)
+        self.lib.ref_float_to_int16_na.argtypes = [_fp, C.c_size_t, C.c_void_p]
+        self.lib.ref_float_to_int16_na(dp, d.size, out.ctypes.data)
+        return out
 
     def minmax1D(self, data, simd=1):
         d, dp = _f32(data)

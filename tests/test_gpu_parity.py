@@ -437,6 +437,36 @@ def test_minmax1D_parity(simd, oracle):
         assert tuple(out.cpu().tolist()) == want
 
 
+def test_int16_converters_parity(simd, oracle):
+    """int16_to_float / float_to_int16 through the C-ABI: bit-exact, host and device buffers,
+    aligned and misaligned starts, saturation."""
+    import torch
+    simd.use_torch_stream()
+    rng = np.random.default_rng(12)
+    for n in (1, 7, 8, 9, 4099, 1_000_003):
+        for off in (0, 1):
+            i16 = rng.integers(-32768, 32768, n + off, dtype=np.int16)[off:]
+            out = np.empty(n, np.float32)
+            simd.lib.int16_to_float(i16.ctypes.data, n, out.ctypes.data)
+            assert np.array_equal(out, oracle.int16_to_float(i16))
+            x = rng.uniform(-40000, 40000, n + off).astype(np.float32)[off:]
+            q = np.empty(n, np.int16)
+            simd.lib.float_to_int16(x.ctypes.data, n, q.ctypes.data)
+            assert np.array_equal(q, oracle.float_to_int16(x))
+    i16 = torch.from_numpy(rng.integers(-32768, 32768, 100000, dtype=np.int16)).cuda()
+    f = torch.empty(100000, device="cuda")
+    simd.lib.int16_to_float(i16.data_ptr(), 100000, f.data_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(f, i16.float())
+    # the chain the converters exist for: int16 PCM in, correlate on device
+    h = uni(5, 200)
+    with simd.Handle(100000, 200, "", True) as hd:
+        y = hd(f, torch.from_numpy(h).cuda())
+        torch.cuda.synchronize()
+    want = oracle.convolve_fft(f.cpu().numpy(), h, 1)
+    check(y.cpu().numpy(), want, f.cpu().numpy(), h, "int16 -> correlate")
+
+
 def test_kernel_launch_counter(simd):
     before = simd.lib.simd_b200_kernel_launches()
     simd.convolve_simd(KAT_X, KAT_H)

@@ -161,3 +161,19 @@ def test_minmax1D_oracle(oracle, reference_or_none):
         if reference_or_none is not None:
             assert reference_or_none.minmax1D(x, 1) == oracle.minmax1D(x)
             assert reference_or_none.minmax1D(x, 0) == oracle.minmax1D(x)
+
+
+def test_int16_converters_oracle(oracle, reference_or_none):
+    """plain casts (inc/simd/arithmetic.h:43-57), bit-exact."""
+    rng = np.random.default_rng(2)
+    i16 = rng.integers(-32768, 32768, 10007, dtype=np.int16)
+    f = oracle.int16_to_float(i16)
+    assert np.array_equal(f, i16.astype(np.float32))
+    x = (rng.uniform(-32768, 32767, 10007)).astype(np.float32)
+    x[:6] = [0.9, -0.9, 1.5, -1.5, 32767.9 - 1, -32768.0]
+    q = oracle.float_to_int16(x)
+    assert np.array_equal(q, np.trunc(x).astype(np.int16))
+    assert oracle.float_to_int16(np.array([1e9, -1e9, np.nan], np.float32)).tolist() == [32767, -32768, 0]
+    if reference_or_none is not None:
+        assert np.array_equal(reference_or_none.int16_to_float(i16), f)
+        assert np.array_equal(reference_or_none.float_to_int16(x), q)

@@ -120,6 +120,10 @@ def _load():
     L.minmax1D.restype = None
     L.simd_b200_minmax1D_device.argtypes = [vp, sz, vp]
     L.simd_b200_minmax1D_device.restype = None
+    L.int16_to_float.argtypes = [vp, sz, vp]
+    L.int16_to_float.restype = None
+    L.float_to_int16.argtypes = [vp, sz, vp]
+    L.float_to_int16.restype = None
     L.simd_b200_filter_noalloc.argtypes = [vp, sz, vp, sz, C.c_int, vp, vp]
     L.simd_b200_filter_noalloc.restype = C.c_int
     L.mallocf.argtypes = [sz]
@@ -149,7 +153,8 @@ EXPORTED_SYMBOLS = (
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
     "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc "
-    "detect_peaks simd_b200_detect_peaks_device minmax1D simd_b200_minmax1D_device").split()
+    "detect_peaks simd_b200_detect_peaks_device minmax1D simd_b200_minmax1D_device "
+    "int16_to_float float_to_int16").split()
 
 
 def _is_torch(a):
