@@ -1,9 +1,10 @@
-/* correlate.c -- plain-C host layer of the cross-correlation API (B200 build).
+/* correlate.c -- cross-correlation entry points of the B200 build.
  *
- * Same structure as the reference (/root/reference/src/correlate.c): the FFT and
- * overlap-save variants are the convolution handles with reverse = 1 (the device kernels
- * then read h in forward order instead of reversed), the brute-force variant is the direct
- * kernel in correlation form.
+ * Cross-correlation is convolution with the impulse response read backwards, and on the
+ * GPU "backwards" is only an index direction inside the kernels' tap loads.  So every
+ * function here is a convolution handle whose `reverse` flag is raised; nothing is copied
+ * or flipped on the host.  The ten symbols and their contracts are those of
+ * /root/reference/inc/simd/correlate.h (implemented there in src/correlate.c:37-160).
  */
 #define LIBSIMD_IMPLEMENTATION
 #include <simd/correlate.h>
@@ -13,97 +14,84 @@
 #include <stdlib.h>
 #include "../csrc/b200_internal.h"
 
-/* reference: src/correlate.c:37-42 */
+/* ---- explicit transform variants: initialise as convolution, then flag ------------------ */
+
+/* src/correlate.c:37-42 */
 CrossCorrelationFFTHandle cross_correlate_fft_initialize(size_t xLength, size_t hLength) {
-  CrossCorrelationFFTHandle handle = convolve_fft_initialize(xLength, hLength);
-  handle.reverse = 1;
-  return handle;
+  CrossCorrelationFFTHandle whole_signal = convolve_fft_initialize(xLength, hLength);
+  whole_signal.reverse = 1;
+  return whole_signal;
 }
 
-/* reference: src/correlate.c:44-48 */
+/* src/correlate.c:54-60 */
+CrossCorrelationOverlapSaveHandle cross_correlate_overlap_save_initialize(size_t xLength,
+                                                                          size_t hLength) {
+  CrossCorrelationOverlapSaveHandle segmented = convolve_overlap_save_initialize(xLength, hLength);
+  segmented.reverse = 1;
+  return segmented;
+}
+
+/* src/correlate.c:44-48 and :62-67 -- the flag travels inside the by-value struct */
 void cross_correlate_fft(CrossCorrelationFFTHandle handle, const float *x, const float *h,
                          float *result) {
   convolve_fft(handle, x, h, result);
 }
 
-/* reference: src/correlate.c:50-52 */
-void cross_correlate_fft_finalize(CrossCorrelationFFTHandle handle) {
-  convolve_fft_finalize(handle);
-}
-
-/* reference: src/correlate.c:54-60 */
-CrossCorrelationOverlapSaveHandle cross_correlate_overlap_save_initialize(size_t xLength,
-                                                                          size_t hLength) {
-  CrossCorrelationOverlapSaveHandle handle =
-      convolve_overlap_save_initialize(xLength, hLength);
-  handle.reverse = 1;
-  return handle;
-}
-
-/* reference: src/correlate.c:62-67 */
 void cross_correlate_overlap_save(CrossCorrelationOverlapSaveHandle handle,
                                   const float *__restrict x, const float *__restrict h,
                                   float *result) {
   convolve_overlap_save(handle, x, h, result);
 }
 
-/* reference: src/correlate.c:69-72 */
+/* src/correlate.c:50-52 and :69-72 */
+void cross_correlate_fft_finalize(CrossCorrelationFFTHandle handle) {
+  convolve_fft_finalize(handle);
+}
+
 void cross_correlate_overlap_save_finalize(CrossCorrelationOverlapSaveHandle handle) {
   convolve_overlap_save_finalize(handle);
 }
 
-/* reference: src/correlate.c:74-126 */
+/* ---- direct kernel in correlation form (src/correlate.c:74-126) ------------------------- */
+
 void cross_correlate_simd(int simd, const float *__restrict x, size_t xLength,
                           const float *__restrict h, size_t hLength,
                           float *__restrict result) {
-  (void)simd;
-  if (!x || !h || !result || xLength == 0 || hLength == 0) {
-    fprintf(stderr, "libSimd(b200): cross_correlate_simd: null pointer or zero length\n");
+  (void)simd;                      /* both values run the GPU kernel */
+  if (x == NULL || h == NULL || result == NULL || xLength == 0 || hLength == 0) {
+    fprintf(stderr, "libSimd(b200): precondition failed: cross_correlate_simd needs non-null "
+                    "pointers and non-zero lengths\n");
     abort();
   }
-  B200Job job;
-  job.x = x; job.x_len = (long long)xLength; job.x_stride = (long long)xLength;
-  job.h = h; job.h_len = (long long)hLength;
-  job.out = result; job.out_len = (long long)(xLength + hLength - 1);
-  job.out_stride = job.out_len;
-  job.pad = (long long)hLength - 1;
-  job.batch = 1;
-  job.reverse = 1;
+  const long long outputs = (long long)(xLength + hLength - 1);
+  B200Job job = {
+    .x = x, .x_len = (long long)xLength, .x_stride = (long long)xLength,
+    .h = h, .h_len = (long long)hLength,
+    .out = result, .out_len = outputs, .out_stride = outputs,
+    .pad = (long long)hLength - 1, .batch = 1,
+    .reverse = 1,                  /* taps are read in forward order: correlation */
+  };
   b200_run(NULL, B200_ALG_DIRECT, &job);
 }
 
-/* reference: src/correlate.c:128-142 */
+/* ---- best-method handle (src/correlate.c:128-160) --------------------------------------- */
+
 CrossCorrelationHandle cross_correlate_initialize(size_t xLength, size_t hLength) {
-  CrossCorrelationHandle handle = convolve_initialize(xLength, hLength);
-  switch (handle.algorithm) {
-    case kConvolutionAlgorithmFFT:
-      handle.handle.fft.reverse = 1;
-      break;
-    case kConvolutionAlgorithmOverlapSave:
-      handle.handle.os.reverse = 1;
-      break;
-    case kConvolutionAlgorithmBruteForce:
-      break;
-  }
-  return handle;
+  CrossCorrelationHandle best = convolve_initialize(xLength, hLength);
+  /* the inner handle of the chosen transform carries the flag; the direct kernel has no
+   * inner handle and is told at call time */
+  if (best.algorithm == kConvolutionAlgorithmFFT) best.handle.fft.reverse = 1;
+  if (best.algorithm == kConvolutionAlgorithmOverlapSave) best.handle.os.reverse = 1;
+  return best;
 }
 
-/* reference: src/correlate.c:144-156 */
 void cross_correlate(CrossCorrelationHandle handle, const float *__restrict x,
                      const float *__restrict h, float *__restrict result) {
-  switch (handle.algorithm) {
-    case kConvolutionAlgorithmFFT:
-    case kConvolutionAlgorithmOverlapSave:
-      convolve(handle, x, h, result);
-      break;
-    case kConvolutionAlgorithmBruteForce:
-      cross_correlate_simd(1, x, (size_t)handle.x_length, h, (size_t)handle.h_length,
-                           result);
-      break;
+  if (handle.algorithm == kConvolutionAlgorithmBruteForce) {
+    cross_correlate_simd(1, x, (size_t)handle.x_length, h, (size_t)handle.h_length, result);
+  } else {
+    convolve(handle, x, h, result);      /* reverse flag already set on the inner handle */
   }
 }
 
-/* reference: src/correlate.c:158-160 */
-void cross_correlate_finalize(CrossCorrelationHandle handle) {
-  convolve_finalize(handle);
-}
+void cross_correlate_finalize(CrossCorrelationHandle handle) { convolve_finalize(handle); }
