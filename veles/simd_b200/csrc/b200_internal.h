@@ -43,7 +43,6 @@ typedef struct B200Plan B200Plan;   /* opaque; lives behind handle.fft_plan */
 B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len, int n_fft,
                            int real_packed);
 void b200_plan_destroy(B200Plan *plan);
-int b200_plan_n_fft(const B200Plan *plan);
 float *b200_plan_spectrum(const B200Plan *plan);   /* device pointer */
 float *b200_plan_scratch(const B200Plan *plan);    /* device pointer */
 

@@ -24,7 +24,7 @@ struct Staging {        // grow-only device staging for host-pointer callers (tw
 struct Pipe {           // copy streams / events of the host-pointer pipeline
   bool ready = false;
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  cudaEvent_t ev_in[2], ev_comp[2], ev_out[2], ev_h;
+  cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
 };
 
 struct DeviceCtx {
@@ -212,7 +212,6 @@ extern "C" void b200_plan_destroy(B200Plan *plan) {
   delete plan;
 }
 
-extern "C" int b200_plan_n_fft(const B200Plan *plan) { return plan->os.n_fft; }
 extern "C" float *b200_plan_spectrum(const B200Plan *plan) { return (float *)plan->os.spectrum; }
 extern "C" float *b200_plan_scratch(const B200Plan *plan) { return plan->staging.x[0]; }
 
@@ -307,7 +306,6 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
         B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_comp[i], cudaEventDisableTiming));
         B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_out[i], cudaEventDisableTiming));
       }
-      B200_CUDA_CHECK(cudaEventCreateWithFlags(&pipe.ev_h, cudaEventDisableTiming));
       pipe.ready = true;
     }
   }
