@@ -22,9 +22,11 @@
  *
  * c(N) is not monotone in N: transforms up to 2048 points run many CTAs per SM and overlap
  * shared-memory traffic with arithmetic, the 8192/16384-point plans run 2 / 1 CTA per SM. */
-static const struct { int n; double c; } kFusedCost[] = {
-  {256, 111.0}, {512, 147.0}, {1024, 150.0}, {2048, 149.0}, {4096, 192.0}, {8192, 203.0},
-  {16384, 237.0},
+static const struct { int n; double c; double real_ratio; } kFusedCost[] = {
+  /* N, paired cost c(N), cost of a real-packed transform relative to a paired one
+   * (tools/real_ratio.py; 256 / 512 extrapolated from the C3 shape) */
+  {256, 111.0, 1.6}, {512, 147.0, 1.5}, {1024, 150.0, 1.34}, {2048, 149.0, 1.20},
+  {4096, 192.0, 1.12}, {8192, 203.0, 1.39}, {16384, 237.0, 1.35},
 };
 #define B200_DIRECT_US_PER_MAC 4.5e-8
 #define B200_DIRECT_LAUNCH_US 9.0
@@ -61,14 +63,13 @@ int b200_os_pick_n(long long h_len, long long out_len) {
 }
 
 /* Real-packed mode: one real segment of 2N samples per N-point transform.  Its transform
- * costs B200_REAL_COST_RATIO times the paired one (one more shared-memory exchange, two more
- * barriers) but yields 2N - taps + 1 outputs instead of 2(N - taps + 1). */
-#define B200_REAL_COST_RATIO 1.25   /* measured on C4 / C5: 1.24 */
-
-static double real_cost_us(int n, double c, long long h_len, long long out_len, long long batch) {
+ * costs real_ratio times the paired one (one more shared-memory exchange, two more barriers,
+ * twice the coefficient bytes) but yields 2N - taps + 1 outputs instead of 2(N - taps + 1). */
+static double real_cost_us(int n, double c, double ratio, long long h_len, long long out_len,
+                           long long batch) {
   double step = (double)(2 * n - (h_len - 1) - 1);
   double nseg = (double)((out_len + (long long)step - 1) / (long long)step);
-  return B200_FUSED_LAUNCH_US + B200_REAL_COST_RATIO * c * nseg * 2.0 * n * (double)batch / 67.1e6;
+  return B200_FUSED_LAUNCH_US + ratio * c * nseg * 2.0 * n * (double)batch / 67.1e6;
 }
 
 void b200_os_pick_mode(long long h_len, long long out_len, int *n_fft, int *real_packed) {
@@ -86,7 +87,7 @@ void b200_os_pick_mode(long long h_len, long long out_len, int *n_fft, int *real
     int n = kFusedCost[i].n;
     if (h_len > n) continue;                            /* all taps in one transform */
     if (force_n && atoi(force_n) != n) continue;
-    double cost = real_cost_us(n, kFusedCost[i].c, h_len, out_len, 1);
+    double cost = real_cost_us(n, kFusedCost[i].c, kFusedCost[i].real_ratio, h_len, out_len, 1);
     if (cost < best * 0.98) { best = cost; *n_fft = n; *real_packed = 1; }
   }
 }
