@@ -56,9 +56,20 @@ def golden():
     return cases
 
 
+def _ensure_built():
+    """libSimd.so is a build artefact (git-ignored): compile it in-tree when a fresh checkout
+    runs the suite before __graft_entry__.build() did (nvcc cross-compiles without a GPU)."""
+    import subprocess
+    lib = os.path.join(ROOT, "veles", "simd_b200", "libSimd.so")
+    if not os.path.exists(lib):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "veles", "simd_b200"), "--no-print-directory",
+                        "-s"], check=True)
+
+
 @pytest.fixture(scope="session")
 def simd():
     """The product library through its Python binding (C-ABI underneath)."""
+    _ensure_built()
     import veles.simd_b200 as v
     return v
 

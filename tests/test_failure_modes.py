@@ -11,6 +11,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def run_child(code):
+    from conftest import _ensure_built
+    _ensure_built()
     env = dict(os.environ, PYTHONPATH=ROOT)
     return subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env,
                           timeout=300)
