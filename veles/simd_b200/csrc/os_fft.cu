@@ -359,6 +359,12 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
       const unsigned n = bytes - off < 32768u ? bytes - off : 32768u;
       bulk_load(dst + off, src + off, n, bar);
     }
+    // the rest of segment B does not fit beside the transform buffer: at least pull it into
+    // L2 now, so the first pass finds it there instead of in HBM
+    if (need > park_len) {
+      const unsigned rest = (unsigned)(need - park_len) * 4u;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + bytes), "r"(rest) : "memory");
+    }
   };
 
   if (t == 0) mbar_init(bar, 1);
