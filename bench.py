@@ -130,6 +130,8 @@ def cpu_baseline(workload, sample_signals=None, target_s=2.0, threads=0):
     from _oracle import Oracle, Reference, have_reference
     op, batch, x_len, h_len, _ = WORKLOADS[workload]
     cores = os.cpu_count() or 1
+    if threads <= 0:
+        threads = cores           # torchrun exports OMP_NUM_THREADS=1: ask for all cores explicitly
     if x_len > 2 ** 24:           # long single signal: time a 2^24-sample prefix (same h)
         x_len_s, nsig, note = 2 ** 24, 1, f"prefix of 2^24 samples of the signal, h={h_len}"
     else:
