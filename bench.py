@@ -424,11 +424,9 @@ def run_sharded_long_signal(args, v, world, rank, local):
     n_out = (e0 - s0) + (h_len - 1 if rank == world - 1 else 0)
     y = torch.empty((n_out,), device="cuda")
 
-    def compute(x, hh, reverse, left_pad, result_length):
-        return v.filter_shard(x, hh, reverse, left_pad, result_length, out=y)
-
     def step():
-        sharded.filter_long_signal(x_local, h, x_len, rank, world, compute, ext=ext)
+        sharded.filter_long_signal(x_local, h, x_len, rank, world, sharded.gpu_compute, ext=ext, out=y,
+                                   overlap=bool(os.environ.get("VELES_B200_OVERLAP_HALO")))
 
     for _ in range(args.warmup):
         step()

@@ -22,7 +22,7 @@ def _free_port():
     return p
 
 
-def _oracle_compute(x, h, reverse, left_pad, result_length):
+def _oracle_compute(x, h, reverse, left_pad, result_length, out_t=None):
     """result[n] = sum_j g[j] X(n + j - left_pad) via the oracle's full convolution."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from _oracle import Oracle
@@ -33,7 +33,11 @@ def _oracle_compute(x, h, reverse, left_pad, result_length):
     out = np.zeros(result_length, dtype=np.float64)
     n = min(result_length, full.size - off)
     out[:n] = full[off:off + n]
-    return torch.from_numpy(out.astype(np.float32))
+    res = torch.from_numpy(out.astype(np.float32))
+    if out_t is not None:
+        out_t.copy_(res)
+        return out_t
+    return res
 
 
 def _worker(rank, world, port, x_length, hl, reverse, q):

@@ -731,6 +731,13 @@ FC_HD void fwd_first_real(int t, const SegReal &w, const TwBases<P> &tb, float2 
         constexpr int r = decltype(rr)::value;
         v[bitrev(r, ilog2(R))] = xa[r * G::S];
       });
+    } else if (inside) {
+      // inside the signal but not 8-byte aligned: two 4-byte loads, no bounds checks
+      const float *xa = w.x + (w.in0 + 2 * (i64)base);
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        v[bitrev(r, ilog2(R))] = make_float2(xa[2 * r * G::S], xa[2 * r * G::S + 1]);
+      });
     } else {
       static_for<0, R>([&](auto rr) {
         constexpr int r = decltype(rr)::value;

@@ -703,9 +703,11 @@ void b200_os_launch_real(const float2 *tw, float4 *coeffs, int n_fft, const DevJ
   op.tw = tw;
   op.spectrum = reinterpret_cast<const float2 *>(coeffs);
   op.accumulate = 0;
-  // one extra leading sample when pad is odd keeps segment starts on even sample offsets
-  // (8-byte loads of sample pairs) and makes the first useful circular sample even
-  const int e = (int)(job.pad & 1);
+  // One extra leading sample when h_len is even makes the first useful circular sample even,
+  // so every segment's results are whole {2p, 2p+1} pairs (8-byte stores).  For a full
+  // convolution (pad = h_len-1) the segment starts are then even too (8-byte loads); for a
+  // shard with another pad they may be odd, which only costs two 4-byte loads per pair.
+  const int e = (int)((job.h_len - 1) & 1);
   op.in_shift = -job.pad - e;
   op.c_off = (int)job.h_len - 1 + e;
   op.step = (2 * n_fft - op.c_off) & ~1;

@@ -96,8 +96,15 @@ void b200_os_pick_mode(long long h_len, long long out_len, int *n_fft, int *real
 ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_length,
                                                       size_t batch) {
   long long out_len = (long long)x_length + (long long)h_length - 1;
-  double direct = B200_DIRECT_LAUNCH_US +
-                  B200_DIRECT_US_PER_MAC * (double)batch * (double)x_length * (double)h_length;
+  /* direct kernel: throughput term when the grid fills the GPU, otherwise the time of its
+   * waves of 2048-output tiles (one 128-thread CTA does 128 multiply-adds per clock, ~4 CTAs
+   * per SM on 148 SMs) -- a few tiles with a long h are slow however small the total is */
+  double tiles = (double)((out_len + 2047) / 2048) * (double)batch;
+  double waves = (double)((long long)((tiles + 591.0) / 592.0));
+  double per_wave_us = (double)h_length * 8.2e-3;
+  double direct_work = B200_DIRECT_US_PER_MAC * (double)batch * (double)x_length * (double)h_length;
+  if (waves * per_wave_us > direct_work) direct_work = waves * per_wave_us;
+  double direct = B200_DIRECT_LAUNCH_US + direct_work;
   int n = b200_os_pick_n((long long)h_length, out_len);
   double c = 255.0;
   for (unsigned i = 0; i < sizeof(kFusedCost) / sizeof(kFusedCost[0]); i++)
