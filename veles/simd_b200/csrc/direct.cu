@@ -114,7 +114,7 @@ __device__ __forceinline__ void accumulate_taps(float (&acc)[kR], const float *g
 }
 
 // ---- pipelined kernel: all taps fit one staging pass (h_len <= kMaxHC) -------------------
-__global__ void __launch_bounds__(kTPB, 4) direct_kernel(DirectParams p) {
+__global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
   extern __shared__ float4 smem4[];
   float *gs = reinterpret_cast<float *>(smem4);          // hc_max + 16 taps
   float *xbuf0 = gs + p.hc_max + 16;                     // two padded x windows
