@@ -40,7 +40,7 @@ def _oracle_compute(x, h, reverse, left_pad, result_length, out_t=None):
     return res
 
 
-def _worker(rank, world, port, x_length, hl, reverse, q):
+def _worker(rank, world, port, x_length, hl, reverse, q, overlap=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -50,8 +50,11 @@ def _worker(rank, world, port, x_length, hl, reverse, q):
     x = torch.from_numpy(rng.uniform(-1, 1, x_length).astype(np.float32))
     h = torch.from_numpy(rng.uniform(-1, 1, hl).astype(np.float32))
     s, e = sharded.signal_range(x_length, rank, world)
-    part = sharded.filter_long_signal(x[s:e].clone(), h, x_length, rank, world, _oracle_compute,
-                                      reverse=reverse)
+    ext, loc = sharded.alloc_shard(e - s, hl - 1)
+    assert loc.data_ptr() % 16 == 0
+    loc.copy_(x[s:e])
+    part = sharded.filter_long_signal(loc, h, x_length, rank, world, _oracle_compute,
+                                      reverse=reverse, ext=ext, overlap=overlap)
     gathered = [None] * world
     dist.all_gather_object(gathered, part.numpy())
     if rank == 0:
@@ -60,15 +63,16 @@ def _worker(rank, world, port, x_length, hl, reverse, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,x_length,hl,reverse", [(2, 5000, 129, False), (2, 4001, 700, True),
-                                                      (3, 9000, 64, False)])
-def test_long_signal_halo_partition(world, x_length, hl, reverse):
+@pytest.mark.parametrize("world,x_length,hl,reverse,overlap", [(2, 5000, 129, False, False),
+                                                              (2, 4001, 700, True, True),
+                                                              (3, 9000, 64, False, True)])
+def test_long_signal_halo_partition(world, x_length, hl, reverse, overlap):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from _oracle import Oracle, rel_l2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, x_length, hl, reverse, q))
+    procs = [ctx.Process(target=_worker, args=(r, world, port, x_length, hl, reverse, q, overlap))
              for r in range(world)]
     for p in procs:
         p.start()
