@@ -89,6 +89,18 @@ def test_direct_kernel_shapes(simd, oracle, xl, hl):
         check(got, oracle.convolve_f64(x, h, corr), x, h, f"direct {xl}x{hl} corr={corr}")
 
 
+@pytest.mark.parametrize("hl", [2, 3, 4, 5, 6, 15, 16, 17, 18, 19, 20, 31, 33, 47, 1023, 1024, 1025, 1030,
+                                2100])
+def test_direct_kernel_tap_tails(simd, oracle, hl):
+    """Every remainder of the tap loop (it runs in groups of four taps, sixteen per block) and
+    the multi-pass kernel above 1024 taps, at tile-boundary-straddling signal lengths."""
+    for xl in (2040, 4100):
+        x, h = uni(xl + hl, xl), uni(hl, hl)
+        for corr in (False, True):
+            got = simd.convolve_simd(x, h, correlate=corr)
+            check(got, oracle.convolve_f64(x, h, corr), x, h, f"direct {xl}x{hl} corr={corr}")
+
+
 @pytest.mark.parametrize("xl,hl", [(16, 4), (201, 50), (300, 128), (1021, 50), (4099, 129), (9000, 512),
                                    (65536, 512), (20000, 1000), (50000, 2048), (100000, 4096),
                                    (70000, 8192), (100000, 20000), (40000, 12000)])
