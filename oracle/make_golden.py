@@ -124,3 +124,89 @@ out["index"] = np.array(index)
 dst = os.path.join(os.path.dirname(HERE), "tests", "golden", "golden.npz")
 np.savez_compressed(dst, **out)
 print(f"wrote {dst}: {len(cases)} cases, {os.path.getsize(dst)/1e6:.2f} MB")
+
+# ---------------------------------------------------------------------------------------------
+# wavelet fixtures: tests/golden/wavelet.npz, produced by the
+# reference's own wavelet.c (scalar *_na entry points; the AVX entry point where noted).
+# Case name: w|<type>|<order>|<ext>|<level or 0>|<input>, arrays <name>/hi and <name>/lo; the
+# inputs are stored once under in/<input>.
+import hashlib  # noqa: E402
+from _oracle import WAVELET_TYPES, EXTENSIONS  # noqa: E402
+
+wav = {}
+rng = np.random.default_rng(0xDA7)
+inputs = {
+    "ramp32": np.arange(32, dtype=np.float32),                   # tests/wavelet.cc:84-88
+    "ramp512": np.arange(512, dtype=np.float32),                 # tests/wavelet.cc:176-183
+    "uni1000": rng.uniform(-1, 1, 1000).astype(np.float32),
+    "uni4098": rng.uniform(-1, 1, 4098).astype(np.float32),
+}
+for k, a in inputs.items():
+    wav["in/" + k] = a
+
+
+def wadd(tname, order, ename, level, iname, na=True):
+    hi, lo = ref.wavelet_apply(WAVELET_TYPES[tname], order, EXTENSIONS[ename], inputs[iname],
+                               level if level else None, na=na)
+    name = "w|%s|%d|%s|%d|%s%s" % (tname, order, ename, level, iname, "" if na else "|simd")
+    wav[name + "/hi"], wav[name + "/lo"] = hi, lo
+    return hi, lo
+
+
+# known answers of the reference's tests: tests/wavelet.cc:83-108 and :110-166
+hi, lo = wadd("daubechies", 8, "periodic", 0, "ramp32")
+assert abs(lo[0] - 1.42184071797210) < 1e-6 and abs(lo[15] - 28.8405938767906) < 1e-5
+assert abs(hi[13] + 15.5030002317990) < 1e-5
+wadd("daubechies", 8, "periodic", 1, "ramp32")
+# the reference tests' grids: tests/wavelet.cc:262-300
+for tname, orders, levels in (("daubechies", (2, 4, 6, 8, 12, 16), (1, 2, 3, 4)),
+                              ("symlet", (2, 4, 6, 8, 12, 16), (1, 2, 3, 4)),
+                              ("coiflet", (6, 12), (1, 2))):
+    for order in orders:
+        for ename in EXTENSIONS:
+            wadd(tname, order, ename, 0, "ramp512")
+            for level in levels:
+                wadd(tname, order, ename, level, "ramp512")
+# beyond the reference's grid: long filters, every family's last rows, odd tile remainders
+for tname, order in (("daubechies", 20), ("daubechies", 38), ("daubechies", 76), ("symlet", 20),
+                     ("symlet", 46), ("symlet", 64), ("symlet", 74), ("symlet", 76),
+                     ("coiflet", 18), ("coiflet", 24), ("coiflet", 30)):
+    for ename in EXTENSIONS:
+        wadd(tname, order, ename, 0, "uni4098")
+    wadd(tname, order, "periodic", 0, "uni1000")
+    wadd(tname, order, "mirror", 3, "uni1000")
+# the AVX entry point, fed the way the reference's tests feed it (tests/wavelet.cc:184-189,
+# 229-232): prepared source, destinations from wavelet_allocate_destination
+import ctypes as C  # noqa: E402
+_fp = C.POINTER(C.c_float)
+L = ref.lib
+L.wavelet_prepare_array.argtypes = [C.c_int, _fp, C.c_size_t]
+L.wavelet_prepare_array.restype = C.c_void_p
+L.wavelet_allocate_destination.argtypes = [C.c_int, C.c_size_t]
+L.wavelet_allocate_destination.restype = C.c_void_p
+L.wavelet_apply.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+L.wavelet_apply.restype = None
+libc = C.CDLL(None)
+libc.free.argtypes = [C.c_void_p]
+for tname, orders in (("daubechies", (2, 4, 6, 8, 12, 16)), ("symlet", (4, 8, 16)), ("coiflet", (6, 12))):
+    for order in orders:
+        src = inputs["ramp512"]
+        prep = L.wavelet_prepare_array(order, src.ctypes.data_as(_fp), src.size)
+        dhi = L.wavelet_allocate_destination(order, src.size)
+        dlo = L.wavelet_allocate_destination(order, src.size)
+        L.wavelet_apply(WAVELET_TYPES[tname], order, EXTENSIONS["mirror"], prep, src.size, dhi, dlo)
+        name = "w|%s|%d|mirror|0|ramp512|simd" % (tname, order)
+        wav[name + "/hi"] = np.ctypeslib.as_array(C.cast(dhi, _fp), shape=(src.size // 2,)).copy()
+        wav[name + "/lo"] = np.ctypeslib.as_array(C.cast(dlo, _fp), shape=(src.size // 2,)).copy()
+        for ptr in (prep, dhi, dlo):
+            libc.free(ptr)
+# digests of the reference's float table rows: pins the product's generated tables on machines
+# without the reference (the rows themselves are not stored)
+for tname, tid in WAVELET_TYPES.items():
+    table = ref.wavelet_table(tid)
+    step = 6 if tname == "coiflet" else 2
+    wav["digest/" + tname] = np.array([hashlib.sha256(table[k][:(k + 1) * step].tobytes()).hexdigest()
+                                       for k in range(table.shape[0])])
+wdst = os.path.join(os.path.dirname(HERE), "tests", "golden", "wavelet.npz")
+np.savez_compressed(wdst, **wav)
+print(f"wrote {wdst}: {sum(1 for k in wav if k.endswith('/hi'))} cases, {os.path.getsize(wdst)/1e6:.2f} MB")

@@ -54,6 +54,25 @@ class Oracle:
         L.oracle_minmax1D.restype = None
         L.oracle_int16_to_float.argtypes = [C.c_void_p, sz, _fp]
         L.oracle_float_to_int16.argtypes = [_fp, sz, C.c_void_p]
+        L.oracle_wavelet_apply.argtypes = [_fp, C.c_int, C.c_int, _fp, sz, _fp, _fp]
+        L.oracle_wavelet_apply.restype = None
+        L.oracle_stationary_wavelet_apply.argtypes = [_fp, C.c_int, C.c_int, C.c_int, _fp, sz, _fp, _fp]
+        L.oracle_stationary_wavelet_apply.restype = None
+
+    def wavelet_apply(self, row, ext, src, level=None):
+        """(desthi, destlo) of the reference's scalar loops for the lowpass table row `row`
+        (order = row.size); level None = decimated transform, else stationary at that level."""
+        row, rp = _f32(row)
+        src, sp = _f32(src)
+        n_out = src.size // 2 if level is None else src.size
+        hi, lo = np.empty(n_out, np.float32), np.empty(n_out, np.float32)
+        if level is None:
+            self.lib.oracle_wavelet_apply(rp, row.size, int(ext), sp, src.size,
+                                          hi.ctypes.data_as(_fp), lo.ctypes.data_as(_fp))
+        else:
+            self.lib.oracle_stationary_wavelet_apply(rp, row.size, int(level), int(ext), sp, src.size,
+                                                     hi.ctypes.data_as(_fp), lo.ctypes.data_as(_fp))
+        return hi, lo
 
     def _run(self, fn, x, h, *extra):
         x, xp = _f32(x)
@@ -232,6 +251,29 @@ class ExtremumPoint(C.Structure):
     _fields_ = [("position", C.c_int), ("value", C.c_float)]
 
 
+WAVELET_TYPES = {"daubechies": 0, "coiflet": 1, "symlet": 2}   # wavelet_types.h:38-42
+EXTENSIONS = {"periodic": 0, "mirror": 1, "constant": 2, "zero": 3}   # wavelet_types.h:44-53
+
+
+def call_wavelet(lib, type_, order, ext, src, level=None, na=True):
+    """wavelet_apply[_na] / stationary_wavelet_apply[_na] through the reference C signatures
+    (inc/simd/wavelet.h:81-162) on any library exporting them; host arrays."""
+    src, sp = _f32(src)
+    n_out = src.size // 2 if level is None else src.size
+    hi, lo = np.empty(n_out, np.float32), np.empty(n_out, np.float32)
+    name = ("wavelet_apply" if level is None else "stationary_wavelet_apply") + ("_na" if na else "")
+    fn = getattr(lib, name)
+    fn.restype = None
+    if level is None:
+        fn.argtypes = [C.c_int, C.c_int, C.c_int, _fp, C.c_size_t, _fp, _fp]
+        fn(int(type_), int(order), int(ext), sp, src.size, hi.ctypes.data_as(_fp), lo.ctypes.data_as(_fp))
+    else:
+        fn.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _fp, C.c_size_t, _fp, _fp]
+        fn(int(type_), int(order), int(level), int(ext), sp, src.size,
+           hi.ctypes.data_as(_fp), lo.ctypes.data_as(_fp))
+    return hi, lo
+
+
 def call_detect_peaks(lib, data, type_=3, simd=0):
     """detect_peaks through the reference C signature on any library exporting it."""
     d, dp = _f32(data)
@@ -297,6 +339,15 @@ class Reference(SimdAPI):
         mn, mx = C.c_float(), C.c_float()
         self.lib.minmax1D(int(simd), dp, d.size, C.byref(mn), C.byref(mx))
         return mn.value, mx.value
+
+    def wavelet_apply(self, type_, order, ext, src, level=None, na=True):
+        return call_wavelet(self.lib, type_, order, ext, src, level, na)
+
+    def wavelet_table(self, type_):
+        """The reference's own float table of one family (rows x taps), read from the library."""
+        name, rows, width = {0: ("kDaubechiesF", 38, 76), 1: ("kCoifletsF", 5, 30),
+                             2: ("kSymletsF", 38, 76)}[int(type_)]
+        return np.ctypeslib.as_array((C.c_float * width * rows).in_dll(self.lib, name)).copy()
 
     def struct_layout(self):
         arr = (C.c_size_t * 16)()
