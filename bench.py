@@ -43,6 +43,8 @@ WORKLOADS = {
     # SURVEY 8(f) rank 1 (not a BASELINE config): extrema of a 2^28-sample series
     "peaks": ("detect_peaks", 1, 2 ** 28, 0, "detect_peaks (both kinds) on 2^28 uniform random samples"),
     "minmax": ("minmax1D", 1, 2 ** 28, 0, "minmax1D on 2^28 uniform random samples"),
+    # one decimated transform level, Daubechies 8 taps, periodic extension
+    "wavelet": ("wavelet_apply", 1, 2 ** 28, 8, "wavelet_apply Daubechies-8, periodic, 2^28 uniform random samples"),
 }
 FP32_PEAK_TFLOPS = 72.1   # measured on this pool's B200 (tools/ffma_peak, profiles/ffma_peak_r01.json)
 
@@ -238,6 +240,8 @@ def main():
         return run_detect_peaks(args, v, world, rank)
     if args.workload == "minmax":
         return run_minmax(args, v, world, rank)
+    if args.workload == "wavelet":
+        return run_wavelet(args, v, world, rank)
     g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
     x = torch.rand((batch, x_len), generator=g, device="cuda") * 2 - 1
     h = torch.rand((h_len,), generator=g, device="cuda") * 2 - 1
@@ -554,6 +558,71 @@ def run_minmax(args, v, world, rank):
                          "frac": ach / peaks["hbm_gbs"], "traffic": None,
                          "kernel": "minmax_partial_kernel (+ one-CTA final)",
                          "algorithmic_bytes_per_launch": 4.0 * size},
+            "cpu_baseline": base, "clocks": None}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def run_wavelet(args, v, world, rank):
+    """wavelet_apply, device-resident: value = input samples/s; algorithmic bytes = 8 per
+    input sample (read once, two half-length outputs written once)."""
+    import numpy as np
+    import torch
+    _, _, size, order, desc = WORKLOADS["wavelet"]
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
+    data = torch.rand((size,), generator=g, device="cuda") * 2 - 1
+    hi = torch.empty(size // 2, device="cuda")
+    lo = torch.empty(size // 2, device="cuda")
+    call = lambda: v.lib.wavelet_apply(v.WAVELET_DAUBECHIES, order, v.EXTENSION_PERIODIC, data.data_ptr(),
+                                       size, hi.data_ptr(), lo.data_ptr())
+    for _ in range(args.warmup):
+        call()
+    torch.cuda.synchronize()
+    launches0 = v.lib.simd_b200_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    # orthonormal pair + periodic extension: the transform keeps the energy
+    e_in = float((data.double() ** 2).sum())
+    e_out = float((hi.double() ** 2).sum() + (lo.double() ** 2).sum())
+    assert abs(e_out / e_in - 1) < 1e-5, (e_in, e_out)
+    peaks, _ = load_peaks()
+    ach = 8.0 * size / (ms * 1e-3) / 1e9
+    base = None
+    if not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from _oracle import Oracle, Reference, have_reference
+        sample = np.random.default_rng(1).uniform(-1, 1, 2 ** 22).astype(np.float32)
+        if have_reference():
+            ref, kind = Reference(), "reference"
+            run = lambda: ref.wavelet_apply(0, order, 0, sample, na=True)
+            how = "wavelet_apply_na (scalar loop; the AVX entry point needs its prepared layout)"
+        else:
+            orc, kind = Oracle(), "port"
+            row = v.wavelet_filters(v.WAVELET_DAUBECHIES, order)[1]
+            run = lambda: orc.wavelet_apply(row, 0, sample)
+            how = "C restatement of wavelet_apply_na"
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 2.0:
+            run()
+            reps += 1
+        dt = time.perf_counter() - t0
+        base = {"value": reps * sample.size / dt / 1e9, "unit": "GSamples/s", "cores": 1, "kind": kind,
+                "sample": f"2^22 samples, {reps} repetitions in {dt:.2f} s, single thread, {how}"}
+    line = {"metric": "wavelet_input_gsamples_per_s", "value": size / (ms * 1e-3) / 1e9,
+            "unit": "GSamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": f"wavelet: {desc}",
+                                                             "l2": "inputs larger than L2"},
+            "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0), "e2e": None,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": ach / peaks["hbm_gbs"], "traffic": None,
+                         "kernel": "wavelet_decimated_kernel",
+                         "algorithmic_bytes_per_launch": 8.0 * size},
             "cpu_baseline": base, "clocks": None}
     if rank == 0:
         print(json.dumps(line), flush=True)

@@ -126,6 +126,22 @@ def _load():
     L.float_to_int16.restype = None
     L.simd_b200_filter_noalloc.argtypes = [vp, sz, vp, sz, C.c_int, vp, vp]
     L.simd_b200_filter_noalloc.restype = C.c_int
+    L.wavelet_validate_order.argtypes = [C.c_int, C.c_int]
+    L.wavelet_validate_order.restype = C.c_int
+    L.wavelet_prepare_array.argtypes = [C.c_int, vp, sz]
+    L.wavelet_prepare_array.restype = vp
+    L.wavelet_allocate_destination.argtypes = [C.c_int, sz]
+    L.wavelet_allocate_destination.restype = vp
+    L.wavelet_recycle_source.argtypes = [C.c_int, vp, sz] + [C.POINTER(vp)] * 4
+    L.wavelet_recycle_source.restype = None
+    for name in ("wavelet_apply", "wavelet_apply_na"):
+        getattr(L, name).argtypes = [C.c_int, C.c_int, C.c_int, vp, sz, vp, vp]
+        getattr(L, name).restype = None
+    for name in ("stationary_wavelet_apply", "stationary_wavelet_apply_na"):
+        getattr(L, name).argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, sz, vp, vp]
+        getattr(L, name).restype = None
+    L.simd_b200_wavelet_filters.argtypes = [C.c_int, C.c_int, vp, vp]
+    L.simd_b200_wavelet_filters.restype = C.c_int
     L.mallocf.argtypes = [sz]
     L.mallocf.restype = vp
     L.malloc_aligned.argtypes = [sz]
@@ -154,7 +170,9 @@ EXPORTED_SYMBOLS = (
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
     "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc "
     "detect_peaks simd_b200_detect_peaks_device minmax1D simd_b200_minmax1D_device "
-    "int16_to_float float_to_int16").split()
+    "int16_to_float float_to_int16 wavelet_validate_order wavelet_prepare_array "
+    "wavelet_allocate_destination wavelet_recycle_source wavelet_apply wavelet_apply_na "
+    "stationary_wavelet_apply stationary_wavelet_apply_na simd_b200_wavelet_filters").split()
 
 
 def _is_torch(a):
@@ -323,6 +341,39 @@ def minmax1D(data, simd=1):
     mn, mx = C.c_float(), C.c_float()
     lib.minmax1D(int(simd), _ptr(data), data.shape[-1], C.byref(mn), C.byref(mx))
     return mn.value, mx.value
+
+
+#: WaveletType / ExtensionType (include/simd/wavelet_types.h)
+WAVELET_DAUBECHIES, WAVELET_COIFLET, WAVELET_SYMLET = 0, 1, 2
+EXTENSION_PERIODIC, EXTENSION_MIRROR, EXTENSION_CONSTANT, EXTENSION_ZERO = 0, 1, 2, 3
+
+
+def wavelet_filters(type_, order):
+    """simd_b200_wavelet_filters: (highpass, lowpass) float32 arrays, or None when (type,
+    order) has no table row."""
+    if order < 1:
+        return None
+    hp, lp = np.empty(order, np.float32), np.empty(order, np.float32)
+    if not lib.simd_b200_wavelet_filters(int(type_), int(order), hp.ctypes.data, lp.ctypes.data):
+        return None
+    return hp, lp
+
+
+def wavelet_apply(type_, order, ext, src, level=None, na=False):
+    """wavelet_apply[_na] (level None) or stationary_wavelet_apply[_na]: (desthi, destlo) of a
+    host (numpy) or device (torch CUDA) series; results live where the input lives."""
+    if not _is_torch(src):
+        src = np.ascontiguousarray(src, dtype=np.float32)
+    n = src.shape[-1]
+    n_out = n // 2 if level is None else n
+    hi, lo = _empty_like(src, (n_out,)), _empty_like(src, (n_out,))
+    if level is None:
+        fn = lib.wavelet_apply_na if na else lib.wavelet_apply
+        fn(int(type_), int(order), int(ext), _ptr(src), n, _ptr(hi), _ptr(lo))
+    else:
+        fn = lib.stationary_wavelet_apply_na if na else lib.stationary_wavelet_apply
+        fn(int(type_), int(order), int(level), int(ext), _ptr(src), n, _ptr(hi), _ptr(lo))
+    return hi, lo
 
 
 def detect_peaks(data, type_=EXTREMUM_BOTH, simd=1):
