@@ -13,10 +13,9 @@
 // plus the (order-1)*dil samples the last output reaches past them) is staged in shared
 // memory once, extension applied while staging, so the tap loop has no bounds logic.  For
 // the decimated transform the window is stored de-interleaved -- even samples in one array,
-// odd samples in another -- so that consecutive lanes (consecutive outputs) read consecutive
-// words for every tap: no bank conflicts, and the global loads are 16-byte.  Every thread
-// owns kR outputs strided by the CTA size, so the stores are fully coalesced.  The two
-// filters ride in the kernel parameters (constant bank).
+// odd samples in another -- so that outputs i, i+1, ... read consecutive words for every tap:
+// 16-byte conflict-free shared-memory reads into a sliding register window, 16-byte global
+// loads and stores.  The two filters ride in the kernel parameters (constant bank).
 //
 // Roofline: 4 B read + 4 B written per input sample (decimated: two half-length outputs;
 // stationary: 4 B read + 8 B written), `order` (stationary: 2*order) FMAs per sample ->
@@ -60,12 +59,26 @@ __device__ __forceinline__ float sample(const WaveletParams &p, i64 n) {
 }
 
 // ---- decimated transform --------------------------------------------------------------------
+// Every thread owns two groups of four consecutive outputs.  Four consecutive outputs and four
+// consecutive tap pairs touch seven consecutive words of each parity array, so one 16-byte
+// shared-memory read per array and group feeds 32 FMAs: the tap loop is bound by the FP32 pipe,
+// not by shared-memory bandwidth, for long filters too.
+constexpr int kGroup = 4;                              // consecutive outputs per group
+constexpr int kGroups = kR / kGroup;                   // groups per thread
+constexpr int kGroupStride = kThreads * kGroup;        // outputs between a thread's groups
+
+__device__ __forceinline__ void load4(float (&w)[8], int at, const float *src) {
+  const float4 v = *reinterpret_cast<const float4 *>(src);
+  w[at] = v.x; w[at + 1] = v.y; w[at + 2] = v.z; w[at + 3] = v.w;
+}
+
 __global__ void __launch_bounds__(kThreads) wavelet_decimated_kernel(const __grid_constant__ WaveletParams p) {
   extern __shared__ float4 smem4[];
-  const int half = kTile + p.order / 2;          // words per parity array (order is even)
-  const int pitch = (half + 35) & ~31;           // + 16 mod 32: the two arrays sit on different banks
+  const int npairs = p.order / 2;                // tap pairs (order is even)
+  const int half = kTile + ((npairs + 3) & ~3) + 4;   // words per parity array incl. window slack
+  const int pitch = (half + 3) & ~3;
   float *ev = reinterpret_cast<float *>(smem4);  // ev[j] = S(base + 2j)
-  float *od = ev + pitch + 16;                   // od[j] = S(base + 2j + 1)
+  float *od = ev + pitch;                        // od[j] = S(base + 2j + 1)
   const int tid = threadIdx.x;
   const i64 out0 = (i64)blockIdx.x * kTile;
   const i64 base = 2 * out0;
@@ -73,16 +86,12 @@ __global__ void __launch_bounds__(kThreads) wavelet_decimated_kernel(const __gri
 
   const bool aligned = ((reinterpret_cast<unsigned long long>(p.src) & 15ull) == 0);
   if (aligned && base + 2 * (i64)pairs <= p.length) {
-    // two pairs per 16-byte load
+    // two pairs per 16-byte load (pairs is a multiple of 4)
     const float4 *s4 = reinterpret_cast<const float4 *>(p.src + base);
     for (int q = tid; q < pairs / 2; q += kThreads) {
       const float4 v = s4[q];
       *reinterpret_cast<float2 *>(ev + 2 * q) = make_float2(v.x, v.z);
       *reinterpret_cast<float2 *>(od + 2 * q) = make_float2(v.y, v.w);
-    }
-    if ((pairs & 1) && tid == 0) {
-      ev[pairs - 1] = p.src[base + 2 * (pairs - 1)];
-      od[pairs - 1] = p.src[base + 2 * (pairs - 1) + 1];
     }
   } else {
     for (int q = tid; q < pairs; q += kThreads) {
@@ -93,25 +102,46 @@ __global__ void __launch_bounds__(kThreads) wavelet_decimated_kernel(const __gri
   }
   __syncthreads();
 
-  float ah[kR], al[kR];
+  const bool vec = ((reinterpret_cast<unsigned long long>(p.hi) | reinterpret_cast<unsigned long long>(p.lo)) & 15ull) == 0;
+  // one group at a time: 24 live floats per thread keep six CTAs on an SM
+#pragma unroll 1
+  for (int g = 0; g < kGroups; g++) {
+    const float *e0 = ev + g * kGroupStride + kGroup * tid, *o0 = od + g * kGroupStride + kGroup * tid;
+    float ah[kGroup], al[kGroup], we[8], wo[8];
 #pragma unroll
-  for (int r = 0; r < kR; r++) ah[r] = al[r] = 0.f;
-  const float *a = ev + tid, *b = od + tid;
-  for (int k = 0; k < p.order; k += 2, a++, b++) {
-    const float h0 = p.hp[k], l0 = p.lp[k], h1 = p.hp[k + 1], l1 = p.lp[k + 1];
+    for (int j = 0; j < kGroup; j++) ah[j] = al[j] = 0.f;
+    load4(we, 0, e0);
+    load4(wo, 0, o0);
+    for (int q0 = 0; q0 < npairs; q0 += 4) {
+      load4(we, 4, e0 + q0 + 4);
+      load4(wo, 4, o0 + q0 + 4);
 #pragma unroll
-    for (int r = 0; r < kR; r++) {
-      const float va = a[r * kThreads], vb = b[r * kThreads];
-      ah[r] = fmaf(h0, va, ah[r]);
-      al[r] = fmaf(l0, va, al[r]);
-      ah[r] = fmaf(h1, vb, ah[r]);
-      al[r] = fmaf(l1, vb, al[r]);
+      for (int qq = 0; qq < 4; qq++) {
+        if (q0 + qq < npairs) {                  // warp-uniform; taps ascend as in the reference
+          const int k = 2 * (q0 + qq);
+          const float h0 = p.hp[k], l0 = p.lp[k], h1 = p.hp[k + 1], l1 = p.lp[k + 1];
+#pragma unroll
+          for (int j = 0; j < kGroup; j++) {
+            ah[j] = fmaf(h0, we[j + qq], ah[j]);
+            al[j] = fmaf(l0, we[j + qq], al[j]);
+            ah[j] = fmaf(h1, wo[j + qq], ah[j]);
+            al[j] = fmaf(l1, wo[j + qq], al[j]);
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { we[j] = we[j + 4]; wo[j] = wo[j + 4]; }
     }
-  }
+    const i64 i = out0 + g * kGroupStride + kGroup * tid;
+    if (vec && i + kGroup <= p.n_out) {
+      *reinterpret_cast<float4 *>(p.hi + i) = make_float4(ah[0], ah[1], ah[2], ah[3]);
+      *reinterpret_cast<float4 *>(p.lo + i) = make_float4(al[0], al[1], al[2], al[3]);
+    } else {
 #pragma unroll
-  for (int r = 0; r < kR; r++) {
-    const i64 i = out0 + tid + r * kThreads;
-    if (i < p.n_out) { p.hi[i] = ah[r]; p.lo[i] = al[r]; }
+      for (int j = 0; j < kGroup; j++) {
+        if (i + j < p.n_out) { p.hi[i + j] = ah[j]; p.lo[i + j] = al[j]; }
+      }
+    }
   }
 }
 
@@ -187,9 +217,8 @@ void wavelet_launch(const WaveletParams &p, bool decimate, cudaStream_t stream) 
   const i64 tiles = (p.n_out + kTile - 1) / kTile;
   B200_REQUIRE(tiles < 2147483647LL, "wavelet grid too large");
   if (decimate) {
-    const int half = kTile + p.order / 2;
-    const int pitch = (half + 35) & ~31;
-    const size_t smem = sizeof(float) * (size_t)(2 * pitch + 32);
+    const int half = kTile + ((p.order / 2 + 3) & ~3) + 4;
+    const size_t smem = sizeof(float) * (size_t)(2 * ((half + 3) & ~3));
     wavelet_decimated_kernel<<<(unsigned)tiles, kThreads, smem, stream>>>(p);
   } else if (p.halo <= kMaxHalo) {
     const size_t smem = sizeof(float) * (size_t)(kTile + p.halo + 4);
