@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """tools/stress.py [seconds] -- randomized parity sweep on the GPU: random shapes through
 every entry-point family (direct, overlap-save, FFT, best handle, batch, shard, no-alloc,
-real-packed forced, host and device pointers) against the CPU oracle.  Prints a summary and
+real-packed forced, wavelet transform, host and device pointers) against the CPU oracle.  Prints a summary and
 exits non-zero at the first mismatch."""
 import os
 import sys
@@ -95,5 +95,23 @@ while time.time() < t_end:
             yb = host(hd(xba, ha))
         for b in (0, B - 1):
             check(yb[b], xb[b], h, corr, "batch")
+    # wavelet transform: random family / order / extension / level on a random even length
+    fam = int(rng.integers(0, 3))
+    order = int(rng.integers(1, 6)) * 6 if fam == 1 else int(rng.integers(1, 39)) * 2
+    ext = int(rng.integers(0, 4))
+    wl = max(2, int(2 ** rng.uniform(1, 17)) & ~1)
+    level = None if rng.integers(0, 2) else int(rng.integers(1, 7))
+    w = rng.uniform(-1, 1, wl).astype(np.float32)
+    hp, lp = v.wavelet_filters(fam, order)
+    want_hi, want_lo = o.wavelet_apply(lp, ext, w, level)
+    wa = torch.from_numpy(w).cuda() if dev else w
+    hi, lo = v.wavelet_apply(fam, order, ext, wa, level)
+    for got, want, filt in ((host(hi), want_hi, hp), (host(lo), want_lo, lp)):
+        scale = float(np.abs(filt).sum())
+        err = float(np.abs(got.astype(np.float64) - want).max())
+        r = float(np.linalg.norm(got.astype(np.float64) - want) / max(np.linalg.norm(want), 1e-30))
+        if not (err <= 1e-4 * scale and (r <= 1e-5 or err <= 2 * order * 2.0 ** -24 * scale)):
+            print("MISMATCH wavelet", fam, order, ext, wl, level, r, err)
+            sys.exit(1)
     n_cases += 1
 print(f"stress OK: {n_cases} random shapes, worst rel-L2 {worst:.2e}")
