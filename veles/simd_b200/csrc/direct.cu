@@ -190,6 +190,71 @@ __global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
   }
 }
 
+// ---- small problems: fewer outputs per thread, more CTAs ---------------------------------------
+// A single short signal gives the pipelined kernel only a handful of 2048-output tiles: a few
+// SMs work through 16 outputs x h_len taps per thread while the rest idle, and the call is
+// bound by that serial chain.  Here a CTA owns kSmallTile = 512 outputs, four consecutive ones
+// per thread: four outputs and four taps touch seven consecutive window words, so one 16-byte
+// shared-memory read feeds 16 FMAs from a sliding 8-word register window; one staging pass,
+// no pipeline.  Same summation order per output as direct_kernel (taps ascending).
+constexpr int kSmallR = 4;
+constexpr int kSmallTile = kSmallR * kTPB;
+
+__global__ void __launch_bounds__(kTPB) direct_small_kernel(DirectParams p) {
+  extern __shared__ float4 smem4[];
+  const int hc = (int)p.h_len;
+  const int hc4 = (hc + 3) & ~3;
+  float *gs = reinterpret_cast<float *>(smem4);          // hc4 taps (zero beyond hc: never read)
+  float *xs = gs + hc4;                                  // kSmallTile + hc4 + 4 window words
+
+  const int tid = threadIdx.x;
+  const i64 b = blockIdx.x / p.tiles_per_signal;
+  const i64 n0 = (blockIdx.x % p.tiles_per_signal) * kSmallTile;
+  const float *xb = p.x + b * p.x_stride;
+  const i64 xi0 = n0 - p.pad;
+  const int wlen = kSmallTile + hc4 + 4;
+  for (int q = tid; q < wlen; q += kTPB) {
+    const i64 i = xi0 + q;
+    xs[q] = (i >= 0 && i < p.x_len) ? xb[i] : 0.f;
+  }
+  for (int j = tid; j < hc4; j += kTPB) gs[j] = j < hc ? (p.reverse ? p.h[j] : p.h[p.h_len - 1 - j]) : 0.f;
+  __syncthreads();
+
+  const float *w0 = xs + kSmallR * tid;
+  float acc[kSmallR], w[8];
+#pragma unroll
+  for (int r = 0; r < kSmallR; r++) acc[r] = 0.f;
+  {
+    const float4 v = *reinterpret_cast<const float4 *>(w0);
+    w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+  }
+  for (int j0 = 0; j0 < hc; j0 += 4) {
+    const float4 v = *reinterpret_cast<const float4 *>(w0 + j0 + 4);
+    w[4] = v.x; w[5] = v.y; w[6] = v.z; w[7] = v.w;
+    const float4 g = *reinterpret_cast<const float4 *>(gs + j0);
+    const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+      if (j0 + jj < hc) {                                // warp-uniform: exact tap count
+#pragma unroll
+        for (int r = 0; r < kSmallR; r++) acc[r] = fmaf(gg[jj], w[r + jj], acc[r]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) w[i] = w[i + 4];
+  }
+  float *ob = p.out + b * p.out_stride;
+  const i64 n = n0 + kSmallR * tid;
+  if (n + kSmallR <= p.out_len && ((reinterpret_cast<unsigned long long>(ob + n) & 15ull) == 0)) {
+    *reinterpret_cast<float4 *>(ob + n) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  } else {
+#pragma unroll
+    for (int r = 0; r < kSmallR; r++) {
+      if (n + r < p.out_len) ob[n + r] = acc[r];
+    }
+  }
+}
+
 // ---- unpipelined kernel for very long impulse responses (several staging passes) ---------
 __global__ void __launch_bounds__(kTPB, 4) direct_long_kernel(DirectParams p) {
   extern __shared__ float4 smem4[];
@@ -259,7 +324,16 @@ void b200_direct_launch(const DevJob &job, cudaStream_t stream) {
   p.xbuf_floats = ((kTile + p.hc_max + 32) / 16 + 1) * 20;
   const i64 tiles = p.tiles_per_signal * job.batch;
   b200_prof_begin(B200_PROF_DIRECT, stream);
-  if (job.h_len <= kMaxHC) {
+  if (job.h_len <= kMaxHC && tiles < 148) {
+    // less than one big tile per SM: spread the work over more, smaller CTAs
+    p.strip = 1;
+    p.tiles_per_signal = (job.out_len + kSmallTile - 1) / kSmallTile;
+    p.strips_per_signal = p.tiles_per_signal;
+    const i64 blocks = p.tiles_per_signal * job.batch;
+    const int hc4 = ((int)job.h_len + 3) & ~3;
+    size_t smem = sizeof(float) * (size_t)(hc4 + kSmallTile + hc4 + 4);
+    direct_small_kernel<<<(unsigned)blocks, kTPB, smem, stream>>>(p);
+  } else if (job.h_len <= kMaxHC) {
     // strips long enough to amortise the pipeline prologue, short enough to fill the GPU
     i64 strip = tiles / (148 * 10);
     if (strip < 1) strip = 1;

@@ -102,6 +102,9 @@ ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_
   double tiles = (double)((out_len + 2047) / 2048) * (double)batch;
   double waves = (double)((long long)((tiles + 591.0) / 592.0));
   double per_wave_us = (double)h_length * 8.2e-3;
+  /* fewer tiles than SMs: the small-problem kernel (512-output tiles, 4 outputs per thread)
+   * runs instead; its serial chain per thread is a quarter as long */
+  if (tiles < 148.0 && h_length <= 1024) per_wave_us = (double)h_length * 2.1e-3;
   double direct_work = B200_DIRECT_US_PER_MAC * (double)batch * (double)x_length * (double)h_length;
   if (waves * per_wave_us > direct_work) direct_work = waves * per_wave_us;
   double direct = B200_DIRECT_LAUNCH_US + direct_work;
