@@ -101,6 +101,17 @@ def test_direct_kernel_tap_tails(simd, oracle, hl):
             check(got, oracle.convolve_f64(x, h, corr), x, h, f"direct {xl}x{hl} corr={corr}")
 
 
+@pytest.mark.parametrize("hl", [1, 2, 3, 5, 15, 16, 17, 20, 33, 47, 64, 1023, 1025, 2100])
+def test_direct_pipelined_kernel_tap_tails(simd, oracle, hl):
+    """The same remainders on a signal long enough (>= 148 tiles of 2048 outputs) that the
+    pipelined big-tile kernel runs rather than the small-problem one."""
+    xl = 310001
+    x, h = uni(xl + hl, xl), uni(hl, hl)
+    for corr in (False, True):
+        got = simd.convolve_simd(x, h, correlate=corr)
+        check(got, oracle.convolve_fft(x, h, corr), x, h, f"direct (pipelined) {xl}x{hl} corr={corr}")
+
+
 @pytest.mark.parametrize("xl,hl", [(16, 4), (201, 50), (300, 128), (1021, 50), (4099, 129), (9000, 512),
                                    (65536, 512), (20000, 1000), (50000, 2048), (100000, 4096),
                                    (70000, 8192), (100000, 20000), (40000, 12000)])
