@@ -54,9 +54,9 @@ ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_
 int simd_b200_transform_length(size_t x_length, size_t h_length);
 
 /* ---- stream and device control --------------------------------------------------------
- * The library enqueues on one CUDA stream per process: its own non-blocking stream until
- * simd_b200_set_stream() installs the caller's (a cudaStream_t passed as void*; NULL is the
- * legacy default stream).  Calls whose x, h and result are all device pointers return
+ * The library enqueues on one CUDA stream per device: its own non-blocking stream until
+ * simd_b200_set_stream() installs the caller's for the current device (a cudaStream_t passed
+ * as void*; NULL is the legacy default stream).  Calls whose x, h and result are all device pointers return
  * without waiting; simd_b200_synchronize() waits for the library stream.  The device is
  * whatever cudaSetDevice() made current in the calling thread; a handle must be used on
  * the device it was created on. */

@@ -37,8 +37,8 @@ struct DeviceCtx {
 
 std::mutex g_mu;                 // guards contexts, the shared staging and user stream
 DeviceCtx g_ctx[kMaxDev];
-std::atomic<void *> g_user_stream{nullptr};
-std::atomic<int> g_have_user_stream{0};
+std::atomic<void *> g_user_stream[kMaxDev];       // per device: a stream belongs to one device
+std::atomic<int> g_have_user_stream[kMaxDev];
 std::atomic<long long> g_launches{0};
 
 int current_device() {
@@ -55,8 +55,8 @@ int current_device() {
 }
 
 cudaStream_t current_stream() {
-  if (g_have_user_stream.load()) return (cudaStream_t)g_user_stream.load();
   int dev = current_device();
+  if (g_have_user_stream[dev].load()) return (cudaStream_t)g_user_stream[dev].load();
   std::lock_guard<std::mutex> lock(g_mu);
   if (!g_ctx[dev].own_stream) {
     B200_CUDA_CHECK(cudaStreamCreateWithFlags(&g_ctx[dev].own_stream, cudaStreamNonBlocking));
@@ -145,8 +145,9 @@ extern "C" void b200_profile_collect(double *total_ms, long long *count) {
 extern "C" long long b200_kernel_launches(void) { return g_launches.load(); }
 
 extern "C" void b200_set_stream(void *s) {
-  g_user_stream.store(s);
-  g_have_user_stream.store(1);
+  int dev = current_device();
+  g_user_stream[dev].store(s);
+  g_have_user_stream[dev].store(1);
 }
 
 extern "C" void *b200_get_stream(void) { return (void *)current_stream(); }
@@ -295,6 +296,10 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     ctx_lock = std::unique_lock<std::mutex>(staged_call_mu);
     st = &g_ctx[dev].staging;
   }
+  // the copy streams and events are one set per device: host-pointer calls of different
+  // handles take turns (they would share the PCIe link anyway)
+  static std::mutex pipe_mu[kMaxDev];
+  std::lock_guard<std::mutex> pipe_lock(pipe_mu[dev]);
   Pipe &pipe = g_ctx[dev].pipe;
   {
     std::lock_guard<std::mutex> lock(g_mu);
