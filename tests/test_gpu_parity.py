@@ -377,6 +377,52 @@ def test_real_packed_mode(simd, oracle, monkeypatch):
     monkeypatch.delenv("VELES_B200_REAL")
 
 
+def test_real_packed_many_segments(simd, oracle, monkeypatch):
+    """Real-packed 16384-point transforms over hundreds of segments: odd and even tap counts,
+    a last partial segment, batches with a row pitch that is and is not a multiple of four
+    samples, and the shard primitive with either parity of pad against h - 1."""
+    import torch
+    simd.use_torch_stream()
+    monkeypatch.setenv("VELES_B200_REAL", "1")
+    monkeypatch.setenv("VELES_B200_FORCE_N", "16384")
+    try:
+        for xl, hl in [(15_000_001, 8192), (16_000_000, 8191), (17_000_003, 6001), (12_500_000, 12000),
+                       (10_000_000, 16384)]:
+            x, h = uni(xl % 1000, xl), uni(hl, hl)
+            for corr in (False, True):
+                with simd.Handle(xl, hl, "_overlap_save", corr) as hd:
+                    assert hd.transform_length == 16384
+                    xd, hd_ = torch.from_numpy(x).cuda(), torch.from_numpy(h).cuda()
+                    got = hd(xd, hd_)
+                    torch.cuda.synchronize()
+                check(got.cpu().numpy(), oracle.convolve_fft(x, h, corr), x, h,
+                      f"real-packed long {xl}x{hl} corr={corr}")
+        # batch: 40 signals x 30 segments; pitch 600000 (multiple of 4) and 600001 (not)
+        hl = 8000
+        h = uni(3, hl)
+        for xl in (600000, 600001):
+            xb = uni(xl, 40, xl)
+            with simd.Handle(xl, hl, "") as hd:
+                assert hd.algorithm == 2 and hd.transform_length == 16384
+                yb = hd(torch.from_numpy(xb).cuda(), torch.from_numpy(h).cuda())
+                torch.cuda.synchronize()
+            yb = yb.cpu().numpy()
+            for b in (0, 17, 39):
+                check(yb[b], oracle.convolve_fft(xb[b], h, 0), xb[b], h, f"real-packed batch pitch {xl} row {b}")
+        # shard primitive: pad = 0 with an even tap count -> pad and h-1 differ in parity
+        x = uni(9, 16_000_000)
+        for hl in (8000, 8001):
+            h = uni(hl, hl)
+            full = oracle.convolve_fft(x, h, 0)
+            got = simd.filter_shard(torch.from_numpy(x).cuda(), torch.from_numpy(h).cuda(), 0, 0,
+                                    x.size - hl + 1, algorithm=2)
+            torch.cuda.synchronize()
+            check(got.cpu().numpy(), full[hl - 1:x.size], x, h, f"real-packed shard h={hl}")
+    finally:
+        monkeypatch.delenv("VELES_B200_REAL")
+        monkeypatch.delenv("VELES_B200_FORCE_N")
+
+
 def test_detect_peaks_parity(simd, oracle):
     """detect_peaks through the C-ABI: bit-exact positions and values against the golden
     fixtures (reference scalar loop) and the oracle, host and device input, all three types,
