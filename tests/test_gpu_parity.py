@@ -447,6 +447,14 @@ def test_detect_peaks_parity(simd, oracle):
             assert np.array_equal(got_p, want_p) and np.array_equal(got_v, want_v), (n, t)
             dp, dv = simd.detect_peaks(torch.from_numpy(data).cuda(), t)
             assert np.array_equal(dp, want_p) and np.array_equal(dv, want_v)
+    # smooth series: most tiles hold no extremum and are skipped by the write pass; one with none
+    t_ = np.arange(2_000_000, dtype=np.float64)
+    for data in ((np.sin(t_ * 2e-4) + 0.3 * np.sin(t_ * 7.1e-5)).astype(np.float32),
+                 np.arange(500_000, dtype=np.float32)):
+        for t in (1, 2, 3):
+            want_p, want_v = oracle.detect_peaks(data, t)
+            got_p, got_v = simd.detect_peaks(torch.from_numpy(data).cuda(), t)
+            assert np.array_equal(got_p, want_p) and np.array_equal(got_v, want_v), t
     # device-resident variant, including truncation at capacity
     data = torch.from_numpy(rng.standard_normal(1_000_000).astype(np.float32)).cuda()
     want_p, want_v = oracle.detect_peaks(data.cpu().numpy(), 3)

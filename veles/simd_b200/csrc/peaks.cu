@@ -5,7 +5,8 @@
 //   peaks_scan_kernel    one CTA turns the tile counts into exclusive offsets (+ total)
 //   peaks_write_kernel   every CTA re-classifies its tile and writes {position, value} at
 //                        offset[tile] + its in-tile rank, which keeps the list ordered
-// The series is read twice (8 B per sample) and 8 B are written per extremum: HBM-bound.
+// The series is read twice (8 B per sample; tiles without extrema are not read again) and 8 B
+// are written per extremum: HBM-bound.
 #include "b200_device.cuh"
 #include <mutex>
 
@@ -19,8 +20,16 @@ constexpr int kTile = kThreads * kPerThread;
 // multiple of 8, so two aligned 16-byte loads fetch them when the series itself is 16-byte
 // aligned); its left / right neighbours come from the adjacent lanes by shuffle, the warp's
 // two edge lanes load theirs.  Bit r of the result <=> sample c0 + r is an interior point and
-// an extremum of the requested type.  vals[] receives the 8 samples.
-__device__ __forceinline__ unsigned classify(const float *d, i64 c0, i64 size, int type, bool vec,
+// an extremum of the requested kind (KIND = the reference's bit mask: 1 maxima, 2 minima,
+// 3 both).  vals[] receives the 8 samples.
+//
+// The reference tests (v - prev) * (v - next) > 0 in float arithmetic
+// (/root/reference/src/detect_peaks.c:41-56).  IEEE subtraction and multiplication are exactly
+// odd in each operand, so with the forward differences dd[r] = sample r - sample r-1 that is
+// dd[r] * dd[r+1] < 0 bit for bit: one subtraction per sample instead of two.  A maximum is
+// dd[r] > 0.  Interior points (1 <= i <= size-2) are two mask operations per thread.
+template <int KIND>
+__device__ __forceinline__ unsigned classify(const float *d, i64 c0, i64 size, bool vec,
                                              float (&vals)[kPerThread]) {
   const int lane = threadIdx.x & 31;
   if (vec && c0 + kPerThread <= size) {
@@ -36,18 +45,22 @@ __device__ __forceinline__ unsigned classify(const float *d, i64 c0, i64 size, i
   float right = __shfl_down_sync(0xffffffffu, vals[0], 1);
   if (lane == 0) left = c0 > 0 && c0 - 1 < size ? d[c0 - 1] : 0.f;
   if (lane == 31) right = c0 + kPerThread < size ? d[c0 + kPerThread] : 0.f;
+  float dd[kPerThread + 1];
+  dd[0] = __fsub_rn(vals[0], left);
+#pragma unroll
+  for (int r = 1; r < kPerThread; r++) dd[r] = __fsub_rn(vals[r], vals[r - 1]);
+  dd[kPerThread] = __fsub_rn(right, vals[kPerThread - 1]);
   unsigned m = 0;
 #pragma unroll
   for (int r = 0; r < kPerThread; r++) {
-    const i64 i = c0 + r;
-    const float prev = r == 0 ? left : vals[r - 1];
-    const float next = r == kPerThread - 1 ? right : vals[r + 1];
-    const float d1 = __fsub_rn(vals[r], prev), d2 = __fsub_rn(vals[r], next);
-    const bool interior = i >= 1 && i <= size - 2;
-    if (interior && __fmul_rn(d1, d2) > 0.f) {
-      if ((d1 > 0.f && (type & 1)) || (d1 < 0.f && (type & 2))) m |= 1u << r;
-    }
+    bool e = __fmul_rn(dd[r], dd[r + 1]) < 0.f;
+    if (KIND == 1) e = e && dd[r] > 0.f;
+    if (KIND == 2) e = e && dd[r] < 0.f;
+    m |= (unsigned)e << r;
   }
+  if (c0 == 0) m &= ~1u;                                   // sample 0 is not interior
+  const i64 last = size - 2 - c0;                          // highest interior r of this thread
+  if (last < kPerThread - 1) m &= last < 0 ? 0u : (2u << (int)last) - 1u;
   return m;
 }
 
@@ -77,18 +90,20 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *total, int *smem
   return smem[32 + wid] + inc - v;
 }
 
-__global__ void __launch_bounds__(kThreads) peaks_count_kernel(const float *d, i64 size, int type,
-                                                               bool vec, unsigned *counts) {
-  __shared__ int smem[65];
+// counts[] zeroed before the launch; every warp adds the extrema of its 256 samples to its
+// tile's count (no CTA barrier: the warps of a tile do not wait for one another)
+template <int KIND>
+__global__ void __launch_bounds__(kThreads) peaks_count_kernel(const float *d, i64 size, bool vec,
+                                                               unsigned *counts) {
   const i64 c0 = (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
   float vals[kPerThread];
-  const int c = __popc(classify(d, c0, size, type, vec, vals));
-  int total;
-  block_exclusive_scan(c, &total, smem);
-  if (threadIdx.x == 0) counts[blockIdx.x] = (unsigned)total;
+  const unsigned c = __reduce_add_sync(0xffffffffu, (unsigned)__popc(classify<KIND>(d, c0, size, vec, vals)));
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(counts + blockIdx.x, c);
 }
 
-// exclusive scan of the `n` tile counts (64-bit running sum); grand total to *total
+// exclusive scan of the `n` tile counts (64-bit running sum), eight counts per thread and
+// round; grand total to *total
+constexpr int kScanPer = 8;
 __global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts,
                                                           unsigned long long *offsets, i64 n,
                                                           unsigned long long *total) {
@@ -97,9 +112,15 @@ __global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
-  for (i64 base = 0; base < n; base += 1024) {
-    const i64 i = base + threadIdx.x;
-    const unsigned long long v = i < n ? counts[i] : 0ull;
+  for (i64 base = 0; base < n; base += 1024 * kScanPer) {
+    const i64 i0 = base + (i64)threadIdx.x * kScanPer;
+    unsigned c[kScanPer];
+    unsigned long long v = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPer; k++) {
+      c[k] = i0 + k < n ? counts[i0 + k] : 0u;
+      v += c[k];
+    }
     unsigned long long inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -120,7 +141,12 @@ __global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts
       if (lane == 31) chunk_total = winc;
     }
     __syncthreads();
-    if (i < n) offsets[i] = carry + warp_off[wid] + inc - v;
+    unsigned long long run = carry + warp_off[wid] + inc - v;
+#pragma unroll
+    for (int k = 0; k < kScanPer; k++) {
+      if (i0 + k < n) offsets[i0 + k] = run;
+      run += c[k];
+    }
     __syncthreads();
     if (threadIdx.x == 0) carry += chunk_total;
     __syncthreads();
@@ -128,15 +154,18 @@ __global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts
   if (threadIdx.x == 0) *total = carry;
 }
 
-__global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i64 size, int type,
-                                                               bool vec,
+template <int KIND>
+__global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i64 size,
+                                                               bool vec, const unsigned *counts,
                                                                const unsigned long long *offsets,
                                                                int2 *out, unsigned long long capacity) {
   __shared__ int smem[65];
   __shared__ int2 staged[kTile];          // the tile's points in rank order
+  // nothing to write for this tile (smooth series: most tiles): do not read it a second time
+  if (counts[blockIdx.x] == 0) return;
   const i64 c0 = (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
   float vals[kPerThread];
-  unsigned m = classify(d, c0, size, type, vec, vals);
+  unsigned m = classify<KIND>(d, c0, size, vec, vals);
   int total;
   int rank = block_exclusive_scan(__popc(m), &total, smem);
 #pragma unroll
@@ -181,11 +210,16 @@ unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_ou
     if (!sc.total) B200_CUDA_CHECK(cudaMalloc(&sc.total, sizeof(unsigned long long)));
     sc.tiles_cap = cap;
   }
-  peaks_count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, vec, sc.counts);
+  const int kind = type & 3;            // the reference tests these two bits only
+  if (kind == 0) return 0;
+  auto count_kernel = kind == 1 ? peaks_count_kernel<1> : kind == 2 ? peaks_count_kernel<2> : peaks_count_kernel<3>;
+  auto write_kernel = kind == 1 ? peaks_write_kernel<1> : kind == 2 ? peaks_write_kernel<2> : peaks_write_kernel<3>;
+  B200_CUDA_CHECK(cudaMemsetAsync(sc.counts, 0, sizeof(unsigned) * (size_t)tiles, stream));
+  count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, sc.counts);
   peaks_scan_kernel<<<1, 1024, 0, stream>>>(sc.counts, sc.offsets, tiles, sc.total);
   b200_count_launch(2);
   if (!count_only) {
-    peaks_write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, type, vec, sc.offsets,
+    write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, sc.counts, sc.offsets,
                                                                  d_out, capacity);
     b200_count_launch(1);
   }
