@@ -505,7 +505,7 @@ def run_detect_peaks(args, v, world, rank):
             "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0), "e2e": None,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": ach / peaks["hbm_gbs"], "traffic": None,
-                         "kernel": "peaks_count + peaks_scan + peaks_write (whole call)",
+                         "kernel": "peaks_count + peaks_sums + peaks_write (whole call)",
                          "algorithmic_bytes_per_launch": abytes},
             "cpu_baseline": base, "clocks": None}
     if rank == 0:

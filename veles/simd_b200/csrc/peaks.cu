@@ -1,14 +1,20 @@
 // peaks.cu -- detect_peaks on the GPU: ordered stream compaction of local extrema.
 //
 // Replaces /root/reference/src/detect_peaks.c:41-127.  Three launches:
-//   peaks_count_kernel   every CTA classifies a tile of interior points and stores its count
-//   peaks_scan_kernel    one CTA turns the tile counts into exclusive offsets (+ total)
+//   peaks_count_kernel   every warp classifies its 256 samples and adds its count to its
+//                        tile's (2048 samples) -- one atomic per warp, no barrier
+//   peaks_sums_kernel    sums of the tile counts per group (32 tiles) and per block of groups
+//                        (1024 tiles); a few microseconds
 //   peaks_write_kernel   every CTA re-classifies its tile and writes {position, value} at
-//                        offset[tile] + its in-tile rank, which keeps the list ordered
-// The series is read twice (8 B per sample; tiles without extrema are not read again) and 8 B
-// are written per extremum: HBM-bound.
+//                        offset + in-tile rank, which keeps the list ordered by position; the
+//                        offset is the sum of the block sums before its block, the group sums
+//                        before its group and the tile counts before it in the group (a
+//                        hundred or so small L2 loads by one warp while the samples are in
+//                        flight: no scan over all tiles); tiles without extrema are not read again
+// The series is read twice (8 B per sample) and 8 B are written per extremum: HBM-bound.
 #include "b200_device.cuh"
 #include <mutex>
+#include <vector>
 
 namespace {
 
@@ -101,71 +107,60 @@ __global__ void __launch_bounds__(kThreads) peaks_count_kernel(const float *d, i
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(counts + blockIdx.x, c);
 }
 
-// exclusive scan of the `n` tile counts (64-bit running sum), eight counts per thread and
-// round; grand total to *total
-constexpr int kScanPer = 8;
-__global__ void __launch_bounds__(1024) peaks_scan_kernel(const unsigned *counts,
-                                                          unsigned long long *offsets, i64 n,
-                                                          unsigned long long *total) {
-  __shared__ unsigned long long warp_off[32];
-  __shared__ unsigned long long chunk_total, carry;
+typedef unsigned long long u64;
+constexpr int kGroupTiles = 32;          // tiles per group sum
+constexpr int kBlockTiles = 1024;        // tiles per block sum (32 groups)
+
+// group_sums[g] = sum of the 32 tile counts of group g, block_sums[b] = sum of the 1024 tile
+// counts of block b; one CTA of 1024 threads per block, one warp per group
+__global__ void __launch_bounds__(kBlockTiles) peaks_sums_kernel(const unsigned *counts, i64 tiles,
+                                                                unsigned *group_sums, u64 *block_sums) {
+  __shared__ unsigned warp_sum[kBlockTiles / 32];
+  const i64 tile = (i64)blockIdx.x * kBlockTiles + threadIdx.x;
+  const unsigned c = __reduce_add_sync(0xffffffffu, tile < tiles ? counts[tile] : 0u);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry = 0;
-  __syncthreads();
-  for (i64 base = 0; base < n; base += 1024 * kScanPer) {
-    const i64 i0 = base + (i64)threadIdx.x * kScanPer;
-    unsigned c[kScanPer];
-    unsigned long long v = 0;
-#pragma unroll
-    for (int k = 0; k < kScanPer; k++) {
-      c[k] = i0 + k < n ? counts[i0 + k] : 0u;
-      v += c[k];
-    }
-    unsigned long long inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += u;
-    }
-    if (lane == 31) warp_off[wid] = inc;
-    __syncthreads();
-    if (wid == 0) {
-      const unsigned long long w = warp_off[lane];
-      unsigned long long winc = w;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        unsigned long long u = __shfl_up_sync(0xffffffffu, winc, o);
-        if (lane >= o) winc += u;
-      }
-      warp_off[lane] = winc - w;
-      if (lane == 31) chunk_total = winc;
-    }
-    __syncthreads();
-    unsigned long long run = carry + warp_off[wid] + inc - v;
-#pragma unroll
-    for (int k = 0; k < kScanPer; k++) {
-      if (i0 + k < n) offsets[i0 + k] = run;
-      run += c[k];
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) carry += chunk_total;
-    __syncthreads();
+  if (lane == 0) {
+    warp_sum[wid] = c;
+    if (tile < tiles) group_sums[(i64)blockIdx.x * (kBlockTiles / kGroupTiles) + wid] = c;   // group exists
   }
-  if (threadIdx.x == 0) *total = carry;
+  __syncthreads();
+  if (wid == 0) {
+    u64 v = warp_sum[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) block_sums[blockIdx.x] = v;
+  }
 }
 
 template <int KIND>
 __global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i64 size,
                                                                bool vec, const unsigned *counts,
-                                                               const unsigned long long *offsets,
-                                                               int2 *out, unsigned long long capacity) {
+                                                               const unsigned *group_sums,
+                                                               const u64 *block_sums, int2 *out,
+                                                               u64 capacity) {
   __shared__ int smem[65];
   __shared__ int2 staged[kTile];          // the tile's points in rank order
+  __shared__ u64 s_base;
   // nothing to write for this tile (smooth series: most tiles): do not read it a second time
   if (counts[blockIdx.x] == 0) return;
   const i64 c0 = (i64)blockIdx.x * kTile + (i64)threadIdx.x * kPerThread;
   float vals[kPerThread];
   unsigned m = classify<KIND>(d, c0, size, vec, vals);
+  // last warp: extrema before this tile = blocks before its block + groups before its group
+  // (inside the block) + tiles before it (inside the group)
+  if (threadIdx.x >= kThreads - 32) {
+    const int lane = threadIdx.x & 31;
+    const unsigned tile = blockIdx.x, blk = tile / kBlockTiles, group = tile / kGroupTiles;
+    u64 v = 0;
+    for (unsigned k = lane; k < blk; k += 32) v += block_sums[k];
+    const unsigned g = blk * (kBlockTiles / kGroupTiles) + lane;      // 32 groups per block
+    if (g < group) v += group_sums[g];
+    const unsigned t = group * kGroupTiles + lane;
+    if (t < tile) v += counts[t];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_base = v;
+  }
   int total;
   int rank = block_exclusive_scan(__popc(m), &total, smem);
 #pragma unroll
@@ -174,15 +169,14 @@ __global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i
   }
   __syncthreads();
   // coalesced copy of the compacted tile to its place in the global list
-  const unsigned long long base = offsets[blockIdx.x];
+  const u64 base = s_base;
   for (int k = threadIdx.x; k < total; k += kThreads) {
     if (base + k < capacity) out[base + k] = staged[k];
   }
 }
 
-struct PeakScratch {       // grow-only per-device scratch: tile counts, offsets, total
-  unsigned *counts = nullptr;
-  unsigned long long *offsets = nullptr, *total = nullptr;
+struct PeakScratch {       // grow-only per-device scratch, one allocation:
+  u64 *block_sums = nullptr;      //   [blocks] u64 | [groups] u32 | [tiles] u32
   size_t tiles_cap = 0;
 };
 PeakScratch g_peaks[16];
@@ -197,36 +191,43 @@ unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_ou
   const i64 tiles = (size + kTile - 1) / kTile;
   const bool vec = (((unsigned long long)d_data) & 15ull) == 0;
   B200_REQUIRE(tiles < 2147483647LL && size < 2147483647LL, "series too long for int positions");
+  const int kind = type & 3;            // the reference tests these two bits only
+  if (kind == 0) return 0;
   std::lock_guard<std::mutex> lock(g_peaks_mu);
   PeakScratch &sc = g_peaks[dev];
   if ((size_t)tiles > sc.tiles_cap) {
-    if (sc.counts) {
+    if (sc.block_sums) {
       B200_CUDA_CHECK(cudaDeviceSynchronize());
-      cudaFree(sc.counts); cudaFree(sc.offsets);
+      cudaFree(sc.block_sums);
     }
-    size_t cap = (size_t)tiles + (size_t)tiles / 4 + 64;
-    B200_CUDA_CHECK(cudaMalloc(&sc.counts, sizeof(unsigned) * cap));
-    B200_CUDA_CHECK(cudaMalloc(&sc.offsets, sizeof(unsigned long long) * cap));
-    if (!sc.total) B200_CUDA_CHECK(cudaMalloc(&sc.total, sizeof(unsigned long long)));
+    const size_t cap = (size_t)tiles + (size_t)tiles / 4 + 64;
+    B200_CUDA_CHECK(cudaMalloc(&sc.block_sums, sizeof(u64) * (cap / kBlockTiles + 2) +
+                                                   sizeof(unsigned) * (cap / kGroupTiles + 2) +
+                                                   sizeof(unsigned) * cap));
     sc.tiles_cap = cap;
   }
-  const int kind = type & 3;            // the reference tests these two bits only
-  if (kind == 0) return 0;
+  const size_t blocks = (size_t)((tiles + kBlockTiles - 1) / kBlockTiles);
+  u64 *block_sums = sc.block_sums;
+  unsigned *group_sums = reinterpret_cast<unsigned *>(block_sums + sc.tiles_cap / kBlockTiles + 2);
+  unsigned *counts = group_sums + sc.tiles_cap / kGroupTiles + 2;
   auto count_kernel = kind == 1 ? peaks_count_kernel<1> : kind == 2 ? peaks_count_kernel<2> : peaks_count_kernel<3>;
   auto write_kernel = kind == 1 ? peaks_write_kernel<1> : kind == 2 ? peaks_write_kernel<2> : peaks_write_kernel<3>;
-  B200_CUDA_CHECK(cudaMemsetAsync(sc.counts, 0, sizeof(unsigned) * (size_t)tiles, stream));
-  count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, sc.counts);
-  peaks_scan_kernel<<<1, 1024, 0, stream>>>(sc.counts, sc.offsets, tiles, sc.total);
+  // the tile counts are accumulated atomically: zero them (the sums are plainly written)
+  B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned) * (size_t)tiles, stream));
+  count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, counts);
+  peaks_sums_kernel<<<(unsigned)blocks, kBlockTiles, 0, stream>>>(counts, tiles, group_sums, block_sums);
   b200_count_launch(2);
   if (!count_only) {
-    write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, sc.counts, sc.offsets,
-                                                                 d_out, capacity);
+    write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, counts, group_sums, block_sums,
+                                                           d_out, capacity);
     b200_count_launch(1);
   }
   B200_CUDA_CHECK(cudaGetLastError());
-  unsigned long long total = 0;
-  B200_CUDA_CHECK(cudaMemcpyAsync(&total, sc.total, sizeof(total), cudaMemcpyDeviceToHost, stream));
+  std::vector<u64> host(blocks);
+  B200_CUDA_CHECK(cudaMemcpyAsync(host.data(), block_sums, sizeof(u64) * blocks, cudaMemcpyDeviceToHost, stream));
   B200_CUDA_CHECK(cudaStreamSynchronize(stream));
+  unsigned long long total = 0;
+  for (u64 v : host) total += v;
   return total;
 }
 
