@@ -163,16 +163,22 @@ __global__ void __launch_bounds__(kThreads) peaks_write_kernel(const float *d, i
   }
   int total;
   int rank = block_exclusive_scan(__popc(m), &total, smem);
+  const int pos0 = (int)c0;               // positions fit an int (checked by the host)
+  int2 *slot = staged + rank;
 #pragma unroll
   for (int r = 0; r < kPerThread; r++) {
-    if (m & (1u << r)) staged[rank++] = make_int2((int)(c0 + r), __float_as_int(vals[r]));
+    if (m & (1u << r)) *slot++ = make_int2(pos0 + r, __float_as_int(vals[r]));
   }
   __syncthreads();
-  // coalesced copy of the compacted tile to its place in the global list
+  // coalesced copy of the compacted tile to its place in the global list (clipped once to the
+  // caller's capacity)
   const u64 base = s_base;
-  for (int k = threadIdx.x; k < total; k += kThreads) {
-    if (base + k < capacity) out[base + k] = staged[k];
-  }
+  int limit = total;
+  if (base >= capacity) limit = 0;
+  else if (capacity - base < (u64)total) limit = (int)(capacity - base);
+  int2 *dst = out + base;
+#pragma unroll 4
+  for (int k = threadIdx.x; k < limit; k += kThreads) dst[k] = staged[k];
 }
 
 struct PeakScratch {       // grow-only per-device scratch, one allocation:
