@@ -179,11 +179,31 @@ def _is_torch(a):
     return type(a).__module__.startswith("torch")
 
 
+_installed_stream = {}     # device index -> stream handle last given to the library
+
+
+def _follow_torch_stream(device_index):
+    """The library enqueues on its own non-blocking stream unless told otherwise.  A CUDA
+    tensor's producer (a torch kernel, an NCCL receive that req.wait() ordered) lives on
+    torch's current stream, so work on CUDA tensors must go to that same stream or it can
+    read data that has not landed yet: install it before every such call."""
+    import torch
+    if torch.cuda.current_device() != device_index:
+        raise ValueError(f"tensor on cuda:{device_index} but cuda:{torch.cuda.current_device()} is current "
+                         "(the library works on the calling thread's current device)")
+    handle = torch.cuda.current_stream(device_index).cuda_stream
+    if _installed_stream.get(device_index) != handle:
+        lib.simd_b200_set_stream(C.c_void_p(handle))
+        _installed_stream[device_index] = handle
+
+
 def _ptr(a):
     """Raw address of a numpy array (host) or torch tensor (host or device)."""
     if _is_torch(a):
         # 1-D contiguous, or 2-D with contiguous rows (row stride is passed separately)
         assert a.dtype.is_floating_point and a.element_size() == 4 and a.stride(-1) == 1
+        if a.is_cuda:
+            _follow_torch_stream(a.device.index)
         return a.data_ptr()
     assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
     return a.ctypes.data
@@ -198,9 +218,11 @@ def _empty_like(a, shape):
 
 def use_torch_stream():
     """Make the library enqueue on torch's current CUDA stream (so torch.cuda.Event timing
-    and torch allocator stream-ordering see the kernels)."""
+    and torch allocator stream-ordering see the kernels).  The wrappers in this module do
+    this on their own whenever they are handed a CUDA tensor; raw lib.* calls with
+    data_ptr() arguments need it once per stream change."""
     import torch
-    lib.simd_b200_set_stream(C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    _follow_torch_stream(torch.cuda.current_device())
 
 
 def profile(enable):
