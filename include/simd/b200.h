@@ -110,7 +110,11 @@ void simd_b200_profile_collect(double *total_ms, long long *count) NOTNULL(1, 2)
  *     it later reads), but two calls whose kernels can run at the same time on the GPU
  *     (different streams, or different host threads without ordering) race on it: order
  *     them on one stream or with events.
- * Returns 0 on success, 1 size beyond the built-in maximum, 2 bad argument, 3 CUDA error. */
+ * Returns 0 on success, 1 size beyond the built-in maximum, 2 bad argument, 3 CUDA error
+ * during the one-time set-up (which is then retried by the next call).  A kernel launch
+ * that fails aborts the process with a message, as everywhere else in this library (the
+ * reference's assert convention).  Per-kernel event timing (simd_b200_profile) skips this
+ * entry point, so that it never creates an event. */
 int simd_b200_filter_noalloc(const float *x, size_t x_length, const float *h,
                              size_t h_length, int reverse, float *result, void *cuda_stream);
 

@@ -251,6 +251,44 @@ def test_batch_c4_shape(simd, oracle, reference_or_none):
     torch.cuda.empty_cache()
 
 
+@pytest.mark.parametrize("B,xl,hl,x_pitch,o_pitch", [
+    (3, 40000, 4096, 40000, 44095),      # 4 segments: last pair's B partial; odd result pitch -> every store phase
+    (2, 30001, 4096, 30004, 34096),      # 3 segments (no B in the last pair), x_len not a multiple of 4
+    (5, 13000, 3000, 13000, 16001),      # one pair per signal, A complete, B a handful of outputs
+    (2, 12292, 4097, 12292, 16390),      # h-1 a multiple of 4: no extra leading samples; B = 6 outputs (< 16-byte head)
+    (1, 200000, 2500, 200000, 202499),   # many pairs of one signal
+    (4, 9000, 4096, 9000, 13096),        # segment A already sticks out of the signal
+])
+def test_persistent_kernel_signal_edges(simd, oracle, monkeypatch, B, xl, hl, x_pitch, o_pitch):
+    """N = 16384 paired plan (the persistent Tensor-Memory kernel): first / last pairs of a signal,
+    whose parked input range is partly zeros and whose result segments are partial, for every
+    16-byte phase of the result rows."""
+    import torch
+    simd.use_torch_stream()
+    monkeypatch.setenv("VELES_B200_FORCE_N", "16384")
+    monkeypatch.setenv("VELES_B200_REAL", "0")
+    g = torch.Generator(device="cuda").manual_seed(B * 1000 + hl)
+    xbuf = torch.rand((B, x_pitch), generator=g, device="cuda") * 2 - 1
+    x = xbuf[:, :xl]
+    h = torch.rand((hl,), generator=g, device="cuda") * 2 - 1
+    ybuf = torch.full((B, o_pitch), float("nan"), device="cuda")
+    y = ybuf[:, :xl + hl - 1]
+    hd = simd.ConvolutionHandle()
+    with simd.Handle(xl, hl, "_overlap_save") as inner:
+        assert inner.transform_length == 16384
+        hd.algorithm, hd.x_length, hd.h_length = simd.ALG_OVERLAP_SAVE, xl, hl
+        hd.handle.os = inner.handle
+        simd.lib.convolve_batch(hd, x.data_ptr(), x_pitch, h.data_ptr(), y.data_ptr(), o_pitch, B)
+        torch.cuda.synchronize()
+    hn = h.cpu().numpy()
+    for b in range(B):
+        xb = x[b].cpu().numpy().copy()
+        check(y[b].cpu().numpy(), oracle.convolve_fft(xb, hn), xb, hn, f"row {b}")
+    # nothing written past a row's end
+    if o_pitch > xl + hl - 1:
+        assert torch.isnan(ybuf[:, xl + hl - 1:]).all()
+
+
 def test_long_signal_c5_shape(simd, oracle):
     """BASELINE config 5 at full size: x = 2^30 samples, h = 8192, on one GPU.  Windows of
     the result are checked against a float64 direct convolution of the matching x window."""

@@ -21,7 +21,8 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libSimd.so")
+# VELES_B200_LIB: another build of the same library (A/B timing of two builds on one GPU box)
+LIB_PATH = os.environ.get("VELES_B200_LIB") or os.path.join(_HERE, "libSimd.so")
 
 _fp = C.POINTER(C.c_float)
 

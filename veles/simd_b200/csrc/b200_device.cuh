@@ -71,3 +71,4 @@ void b200_count_launch(int n);
 enum { B200_PROF_DIRECT = 0, B200_PROF_FUSED = 1, B200_PROF_SPECTRUM = 2, B200_PROF_KINDS = 3 };
 void b200_prof_begin(int kind, cudaStream_t stream);
 void b200_prof_end(int kind, cudaStream_t stream);
+void b200_prof_suppress(int on);   // per calling thread

@@ -105,15 +105,20 @@ std::vector<ProfPair> g_prof_pairs;
 cudaEvent_t g_prof_open[B200_PROF_KINDS];
 }  // namespace
 
+// simd_b200_filter_noalloc promises to create no event: it switches profiling off for the
+// calling thread around its launches.
+static thread_local int g_prof_suppressed = 0;
+void b200_prof_suppress(int on) { g_prof_suppressed = on; }
+
 void b200_prof_begin(int kind, cudaStream_t stream) {
-  if (!g_prof_on.load()) return;
+  if (!g_prof_on.load() || g_prof_suppressed) return;
   std::lock_guard<std::mutex> lock(g_prof_mu);
   B200_CUDA_CHECK(cudaEventCreate(&g_prof_open[kind]));
   B200_CUDA_CHECK(cudaEventRecord(g_prof_open[kind], stream));
 }
 
 void b200_prof_end(int kind, cudaStream_t stream) {
-  if (!g_prof_on.load()) return;
+  if (!g_prof_on.load() || g_prof_suppressed) return;
   std::lock_guard<std::mutex> lock(g_prof_mu);
   ProfPair p;
   p.e0 = g_prof_open[kind];

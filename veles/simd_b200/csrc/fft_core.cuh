@@ -344,50 +344,6 @@ FC_HD void fwd_first(int t, const SegPair &w, const TwBases<P> &tb, float2 *sm) 
   });
 }
 
-// forward first pass of the persistent kernel: the contiguous input range of the segment pair
-// x[inA, inA + park_len) was brought into shared memory (`park`) by a bulk copy while the
-// previous pair was being processed.  Segment A lies entirely inside it; segment B starts
-// `step` samples later, so its head does too and only its tail is read from global memory.
-template <class P>
-FC_HD void fwd_first_parked(int t, const SegPair &w, const TwBases<P> &tb, float2 *sm,
-                            const float *park, int park_len, int step, bool wait_store) {
-  constexpr int R = P::R1, NB = P::N;
-  using G = PassGeom<P, NB, R>;
-  static_for<0, P::E / R>([&](auto jj) {
-    constexpr int j = decltype(jj)::value;
-    int base, npp, bf;
-    G::locate(t, j, base, npp, bf);
-    auto *smb = sm + pad_pos(base);
-    float2 v[R];
-    const float *xb = w.x + (w.inB + base);
-    const float *pa = park + base;
-    static_for<0, R>([&](auto rr) {
-      constexpr int r = decltype(rr)::value;
-      const float a = pa[r * G::S];
-      float b;
-      // row r of B (S consecutive samples over the CTA) lies inside the parked range: CTA-uniform
-      if (step + (r + 1) * G::S <= park_len) b = pa[step + r * G::S];
-      else b = xb[r * G::S];
-      v[bitrev(r, ilog2(R))] = make_float2(a, b);
-    });
-    dft_inreg<R, false>(v);
-    if constexpr (G::S > 1) {
-      Powers<R> pw;
-      pw.init(tb.w1[j]);
-      static_for<1, R>([&](auto kk) {
-        constexpr int k = decltype(kk)::value;
-        v[k] = cmul(v[k], pw.template get<k>());
-      });
-    }
-    static_assert(P::E / R == 1, "persistent kernel: one first-pass butterfly per thread");
-    if (wait_store) wait_staged_results_read(t);      // CTA-uniform
-    static_for<0, R>([&](auto kk) {
-      constexpr int k = decltype(kk)::value;
-      smb[G::off(k)] = v[k];
-    });
-  });
-}
-
 // forward middle pass (3-pass plans only): shared -> DFT_R2 -> twiddle -> shared (in place)
 template <class P>
 FC_HD void fwd_mid(int t, const TwBases<P> &tb, float2 *sm) {
@@ -547,37 +503,6 @@ FC_HD void inv_last(int t, const SegPair &w, const TwBases<P> &tb, const float2 
         if (tt < (unsigned)w.cntB) ob[r * G::S] = w.accumulate ? ob[r * G::S] + v[r].y : v[r].y;
       });
     }
-  });
-}
-
-// inverse last pass without the global stores: natural-order circular samples stay in v[]
-// (register j*R + r holds circular index base_j + r*S; .x -> segment A, .y -> segment B).
-template <class P>
-FC_HD void inv_last_regs(int t, const TwBases<P> &tb, const float2 *sm, float2 *v) {
-  constexpr int R = P::R1, NB = P::N;
-  using G = PassGeom<P, NB, R>;
-  static_for<0, P::E / R>([&](auto jj) {
-    constexpr int j = decltype(jj)::value;
-    int base, npp, bf;
-    G::locate(t, j, base, npp, bf);
-    auto *smb = sm + pad_pos(base);
-    float2 *vj = v + j * R;
-    if constexpr (G::S > 1) {
-      Powers<R> pw;
-      pw.init(tb.w1[j]);
-      static_for<0, R>([&](auto kk) {
-        constexpr int k = decltype(kk)::value;
-        float2 e = smb[G::off(k)];
-        if constexpr (k > 0) e = cmul_conj(e, pw.template get<k>());
-        vj[bitrev(k, ilog2(R))] = e;
-      });
-    } else {
-      static_for<0, R>([&](auto kk) {
-        constexpr int k = decltype(kk)::value;
-        vj[bitrev(k, ilog2(R))] = smb[G::off(k)];
-      });
-    }
-    dft_inreg<R, true>(vj);
   });
 }
 

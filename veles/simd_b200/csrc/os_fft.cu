@@ -21,6 +21,7 @@
 // overlap-save), which also serves the whole-signal "FFT" algorithm for long inputs.
 #include "b200_device.cuh"
 #include "fft_core.cuh"
+#include "tmem_store.cuh"
 #include <math.h>
 #include <mutex>
 #include <vector>
@@ -276,16 +277,7 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
   if (live) inv_last_real<P>(t, w, tb, sm);
 }
 
-// ---- persistent variant of the paired kernel for the one-CTA-per-SM plans ------------------
-// One CTA per SM loops over segment pairs.  While a pair is being transformed, a bulk
-// asynchronous copy (cp.async.bulk / TMA, completion on an mbarrier) brings the next pair's
-// input range into the shared memory left over beside the transform buffer, so the next
-// pair's first pass starts from shared memory instead of waiting for HBM, and the current
-// pair's result stores drain while that first pass computes.  Needs 16-byte aligned segment
-// starts (the host picks step and leading-sample count accordingly) -- otherwise, and for
-// pairs that stick out of the signal, the plain kernel's guarded loads are used.
-constexpr int kParkFloats = 20992;      // 82 KiB beside the 136 KiB transform buffer (+ 8 KiB twiddle bases)
-
+// ---- mbarrier / bulk-copy helpers of the persistent kernel ---------------------------------
 __device__ __forceinline__ unsigned smem_u32(const void *p) {
   return (unsigned)__cvta_generic_to_shared(p);
 }
@@ -304,6 +296,9 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned b
       ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
   unsigned ok;
   do {
@@ -315,16 +310,235 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
   } while (!ok);
 }
 
+// ---- passes of the persistent kernel with the twiddle factors kept in Tensor Memory -------
+// Same arithmetic as fwd_first / fwd_mid / inv_mid / inv_last of fft_core.cuh, except that
+// the 31 factors of a butterfly come out of the thread's private TMEM words (tmem_store.cuh)
+// instead of being rebuilt from their base: column 2k, 2k+1 of set 0 holds W_N^(t*k) (first /
+// last pass), of set 1 (64 columns further) W_NB2^((t & 15)*k) (middle passes).  Four x16
+// loads per pass, issued two at a time ahead of their use.
+
+// v[k] *= factor k for k in [8c, 8c+8), k > 0 (forward passes: factors after the butterfly)
+template <int C>
+__device__ __forceinline__ void tm_apply_fwd(float2 *v, const tmem::Chunk &c) {
+  static_for<0, 8>([&](auto ii) {
+    constexpr int i = decltype(ii)::value;
+    constexpr int k = 8 * C + i;
+    if constexpr (k > 0) v[k] = cmul(v[k], c.get(i));
+  });
+}
+// v[bitrev(k)] = e[k] * conj(factor k) (inverse passes: factors before the butterfly)
+template <int C, int R>
+__device__ __forceinline__ void tm_apply_inv(float2 *v, const float2 *e, const tmem::Chunk &c) {
+  static_for<0, 8>([&](auto ii) {
+    constexpr int i = decltype(ii)::value;
+    constexpr int k = 8 * C + i;
+    if constexpr (k > 0) v[bitrev(k, ilog2(R))] = cmul_conj(e[k], c.get(i));
+    else v[0] = e[0];
+  });
+}
+
+__device__ __forceinline__ void tm_twiddle_fwd(float2 *v, unsigned set_addr, tmem::Chunk &a, tmem::Chunk &b) {
+  // a, b hold chunks 0 and 1 (loads issued by the caller before the butterfly)
+  tmem::wait_loads(a, b);
+  tm_apply_fwd<0>(v, a);
+  tmem::load(a, set_addr + 32);
+  tm_apply_fwd<1>(v, b);
+  tmem::load(b, set_addr + 48);
+  tmem::wait_loads(a, b);
+  tm_apply_fwd<2>(v, a);
+  tm_apply_fwd<3>(v, b);
+}
+
+// Forward first pass.  x[inA, inA + park_len) -- zeros where that leaves the signal -- was
+// brought into shared memory (`park`) while the previous pair was being processed: all of
+// segment A and the head of segment B (which starts `step` samples later); the rows of B
+// beyond it come from global memory, bounds-checked when the pair touches the signal's end
+// (`guard`, CTA-uniform).  `before_stores` runs between the arithmetic and the stores into
+// the transform buffer (the previous pair's staged results may still be leaving it).
+template <class P, class F>
+__device__ __forceinline__ void fwd_first_parked_tm(int t, const SegPair &w, float2 *sm, const float *park,
+                                                    int park_len, int step, bool guard, unsigned tw_addr,
+                                                    F &&before_stores) {
+  constexpr int R = P::R1, NB = P::N;
+  static_assert(R == 32 && P::E == R, "one radix-32 butterfly per thread");
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate(t, 0, base, npp, bf);
+  auto *smb = sm + pad_pos(base);
+  float2 v[R];
+  tmem::Chunk a, b;
+  tmem::load(a, tw_addr);
+  tmem::load(b, tw_addr + 16);
+  const float *xb = w.x + (w.inB + base);
+  const i64 left = w.x_len - (w.inB + base);      // samples of the signal from xb on
+  const float *pa = park + base;
+  static_for<0, R>([&](auto rr) {
+    constexpr int r = decltype(rr)::value;
+    const float va = pa[r * G::S];
+    float vb;
+    if (step + (r + 1) * G::S <= park_len) vb = pa[step + r * G::S];   // CTA-uniform
+    else if (!guard) vb = xb[r * G::S];
+    else vb = (i64)(r * G::S) < left ? xb[r * G::S] : 0.0f;
+    v[bitrev(r, ilog2(R))] = make_float2(va, vb);
+  });
+  dft_inreg<R, false>(v);
+  tm_twiddle_fwd(v, tw_addr, a, b);
+  before_stores();
+  static_for<0, R>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    smb[G::off(k)] = v[k];
+  });
+}
+
+// pairs that cannot be parked (nothing of them inside the signal is bulk-copyable)
+template <class P, class F>
+__device__ __forceinline__ void fwd_first_tm(int t, const SegPair &w, float2 *sm, unsigned tw_addr,
+                                             F &&before_stores) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate(t, 0, base, npp, bf);
+  auto *smb = sm + pad_pos(base);
+  float2 v[R];
+  tmem::Chunk a, b;
+  tmem::load(a, tw_addr);
+  tmem::load(b, tw_addr + 16);
+  static_for<0, R>([&](auto rr) {
+    constexpr int r = decltype(rr)::value;
+    const int p = base + r * G::S;
+    const float va = load_x(w.x, w.x_len, w.inA + p);
+    const float vb = w.haveB ? load_x(w.x, w.x_len, w.inB + p) : 0.0f;
+    v[bitrev(r, ilog2(R))] = make_float2(va, vb);
+  });
+  dft_inreg<R, false>(v);
+  tm_twiddle_fwd(v, tw_addr, a, b);
+  before_stores();
+  static_for<0, R>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    smb[G::off(k)] = v[k];
+  });
+}
+
+template <class P>
+__device__ __forceinline__ void fwd_mid_tm(int t, float2 *sm, unsigned tw_addr) {
+  constexpr int R = P::R2, NB = P::NB2;
+  static_assert(R == 32 && P::E == R, "one radix-32 butterfly per thread");
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate_mid(t, 0, base, npp, bf);
+  auto *smb = sm + pad_pos(base);
+  float2 v[R];
+  tmem::Chunk a, b;
+  tmem::load(a, tw_addr + 64);
+  tmem::load(b, tw_addr + 64 + 16);
+  static_for<0, R>([&](auto rr) {
+    constexpr int r = decltype(rr)::value;
+    v[bitrev(r, ilog2(R))] = smb[G::off(r)];
+  });
+  dft_inreg<R, false>(v);
+  tm_twiddle_fwd(v, tw_addr + 64, a, b);
+  static_for<0, R>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    smb[G::off(k)] = v[k];
+  });
+}
+
+// shared -> conj twiddle -> v[] in butterfly input order (both inverse strided passes)
+template <class P, class G, int R>
+__device__ __forceinline__ void tm_load_twiddled_inv(const float2 *smb, float2 *v, unsigned set_addr) {
+  tmem::Chunk a, b;
+  tmem::load(a, set_addr);
+  tmem::load(b, set_addr + 16);
+  float2 e[R];
+  static_for<0, R>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    e[k] = smb[G::off(k)];
+  });
+  tmem::wait_loads(a, b);
+  tm_apply_inv<0, R>(v, e, a);
+  tmem::load(a, set_addr + 32);
+  tm_apply_inv<1, R>(v, e, b);
+  tmem::load(b, set_addr + 48);
+  tmem::wait_loads(a, b);
+  tm_apply_inv<2, R>(v, e, a);
+  tm_apply_inv<3, R>(v, e, b);
+}
+
+template <class P>
+__device__ __forceinline__ void inv_mid_tm(int t, float2 *sm, unsigned tw_addr) {
+  constexpr int R = P::R2, NB = P::NB2;
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate_mid(t, 0, base, npp, bf);
+  auto *smb = sm + pad_pos(base);
+  float2 v[R];
+  tm_load_twiddled_inv<P, G, R>(smb, v, tw_addr + 64);
+  dft_inreg<R, true>(v);
+  static_for<0, R>([&](auto rr) {
+    constexpr int r = decltype(rr)::value;
+    smb[G::off(r)] = v[r];
+  });
+}
+
+template <class P>
+__device__ __forceinline__ void inv_last_regs_tm(int t, const float2 *sm, float2 *v, unsigned tw_addr) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate(t, 0, base, npp, bf);
+  tm_load_twiddled_inv<P, G, R>(sm + pad_pos(base), v, tw_addr);
+  dft_inreg<R, true>(v);
+}
+
+// Once per CTA: every thread writes its two sets of 32 factors, taken straight from the
+// tabulated W_N^j (j < N/2, computed in double on the host) -- no product trees, so each
+// factor is correctly rounded.
+template <class P>
+__device__ __forceinline__ void tm_fill_twiddles(int t, const float2 *tw, unsigned tw_addr) {
+  auto w_pow = [&](int idx) {           // W_N^idx, idx in [0, N)
+    const float2 v = tw[idx & (P::N / 2 - 1)];
+    return (idx & (P::N / 2)) ? make_float2(-v.x, -v.y) : v;
+  };
+  const int n1 = t;                      // first / last pass: butterfly t, stride N/32
+  const int n2 = (t & 15) * P::R1;       // middle passes: W_NB2^(t & 15) = W_N^(R1 * (t & 15))
+  for (int c = 0; c < 4; c++) {
+    tmem::Chunk a, b;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const int k = 8 * c + i;
+      a.set(i, w_pow((n1 * k) & (P::N - 1)));
+      b.set(i, w_pow((n2 * k) & (P::N - 1)));
+    }
+    tmem::store(tw_addr + 16 * c, a);
+    tmem::store(tw_addr + 64 + 16 * c, b);
+  }
+  tmem::wait_stores();
+}
+
+// ---- persistent kernel for the one-CTA-per-SM plan (N = 16384, paired segments) -----------
+// One CTA per SM loops over segment pairs.
+//  * Twiddle factors live in Tensor Memory (filled once per CTA, see above).
+//  * While a pair is being transformed, a bulk asynchronous copy (cp.async.bulk / TMA,
+//    completion on an mbarrier) brings the next pair's input range into the shared memory
+//    left beside the transform buffer, so the next pair's first pass starts from shared
+//    memory instead of waiting for HBM, and the current pair's result stores drain while
+//    that first pass computes.  Needs 16-byte aligned segment starts (the host picks step
+//    and leading-sample count accordingly).  The first and the last pair of a signal stick
+//    out of it: the part of their range that lies outside is zero-filled by the threads, the
+//    part inside is bulk-copied as for every other pair.
+//  * Results leave through shared memory and one bulk store per segment.
+constexpr int kParkFloats = 23040;      // 90 KiB beside the 136 KiB transform buffer
+
 template <class P>
 __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
   extern __shared__ float4 smem4[];
   float2 *sm = reinterpret_cast<float2 *>(smem4);
   float *park = reinterpret_cast<float *>(sm + P::SMEM_FLOAT2);
-  TwBases<P> *tb_sm = reinterpret_cast<TwBases<P> *>(park + kParkFloats);   // one per thread
-  unsigned long long *bar = reinterpret_cast<unsigned long long *>(tb_sm + P::T);
+  unsigned long long *bar = reinterpret_cast<unsigned long long *>(park + kParkFloats);
+  unsigned *tmem_base = reinterpret_cast<unsigned *>(bar + 1);
   const int t = threadIdx.x;
 
-  // parked range of a pair: x[inA, inA + park_len), clipped to what the pair reads
+  // parked range of a pair: X(inA + q), q in [0, park_len), clipped to what the pair reads
   const int need = P::N + p.step;                       // A followed by B's tail
   const int park_len = need < kParkFloats ? need : kParkFloats;
 
@@ -345,35 +559,55 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
     w.c_off = p.c_off;
     w.accumulate = p.accumulate != 0;
   };
-  // a pair can be parked when everything it reads lies inside the signal
-  auto parkable = [&](const SegPair &w) {
-    return w.haveB && w.inA >= 0 && w.inB + P::N <= w.x_len;
+  // The part of the parked range that lies inside the signal, [lo, lo + n) in park indices
+  // (both multiples of 4 floats: segment starts are 16-byte aligned); n <= 0: nothing to copy.
+  auto park_span = [&](const SegPair &w, int &lo, int &n) {
+    lo = w.inA < 0 ? (int)(-w.inA < (i64)park_len ? -w.inA : park_len) : 0;
+    const i64 end = w.x_len - w.inA;                    // first park index past the signal
+    const int hi = end < (i64)park_len ? (int)(end > 0 ? end : 0) : park_len;
+    n = hi > lo ? (hi - lo) & ~3 : 0;
   };
-  auto issue_park = [&](const SegPair &w) {             // one thread
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    const unsigned bytes = (unsigned)park_len * 4u;
-    mbar_expect_tx(bar, bytes);
-    const char *src = reinterpret_cast<const char *>(w.x + w.inA);
-    char *dst = reinterpret_cast<char *>(park);
-    for (unsigned off = 0; off < bytes; off += 32768u) {
-      const unsigned n = bytes - off < 32768u ? bytes - off : 32768u;
-      bulk_load(dst + off, src + off, n, bar);
+  // all threads, after the barrier that ends the reads of the previous parked range
+  auto start_park = [&](const SegPair &w) -> bool {
+    int lo, n;
+    park_span(w, lo, n);
+    if (n <= 0) return false;                           // CTA-uniform
+    if (lo > 0 || lo + n < park_len) {
+      // a signal edge: zeros in front of the signal, zeros (and up to 3 samples the 16-byte
+      // granularity left over) behind it
+      for (int q = t; q < lo; q += P::T) park[q] = 0.0f;
+      for (int q = lo + n + t; q < park_len; q += P::T) park[q] = load_x(w.x, w.x_len, w.inA + q);
     }
-    // the rest of segment B does not fit beside the transform buffer: at least pull it into
-    // L2 now, so the first pass finds it there instead of in HBM
-    if (need > park_len) {
-      const unsigned rest = (unsigned)(need - park_len) * 4u;
-      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + bytes), "r"(rest) : "memory");
+    if (t == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      const unsigned bytes = (unsigned)n * 4u;
+      mbar_expect_tx(bar, bytes);
+      const char *src = reinterpret_cast<const char *>(w.x + (w.inA + lo));
+      char *dst = reinterpret_cast<char *>(park + lo);
+      for (unsigned off = 0; off < bytes; off += 32768u) {
+        const unsigned m = bytes - off < 32768u ? bytes - off : 32768u;
+        bulk_load(dst + off, src + off, m, bar);
+      }
+      // the rest of segment B does not fit beside the transform buffer: at least pull it into
+      // L2 now, so the first pass finds it there instead of in HBM
+      const i64 rest_lo = w.inA + park_len;
+      i64 rest_hi = w.inA + need;
+      if (rest_hi > w.x_len) rest_hi = w.x_len;
+      if (rest_hi > rest_lo) {
+        const unsigned rest = (unsigned)(rest_hi - rest_lo) * 4u & ~15u;
+        if (rest) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(w.x + rest_lo), "r"(rest) : "memory");
+      }
     }
+    return true;
   };
 
   if (t == 0) mbar_init(bar, 1);
-  {
-    TwBases<P> tb0;
-    load_twiddle_bases<P>(t, p.tw, tb0);
-    tb_sm[t] = tb0;             // read back by the same thread only
-  }
+  if (t < 32) tmem::alloc_all(tmem_base);
+  tmem::fence_before_sync();
   __syncthreads();
+  tmem::fence_after_sync();
+  const unsigned tw_addr = tmem::thread_base(*tmem_base, t);
+  tm_fill_twiddles<P>(t, p.tw, tw_addr);
   HRegs<P> hr;
 
   // Loop state is kept small on purpose (the passes need ~124 registers): the pair
@@ -383,9 +617,10 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
   if (item < p.total) {
     SegPair w0;
     pair_of(item, w0);
-    parked = parkable(w0);
-    if (parked && t == 0) issue_park(w0);
+    parked = start_park(w0);
   }
+  __syncthreads();                // zeros the threads wrote into an edge pair's parked range
+                                  // (later pairs: the barriers of the previous pair do this)
   unsigned parity = 0;
   bool store_pending = false;     // a bulk store is still reading staged results from `sm`
   asm volatile("griddepcontrol.wait;" ::: "memory");     // the spectrum kernel is short
@@ -393,14 +628,18 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
     {
       SegPair w;
       pair_of(item, w);
-      const TwBases<P> tb = tb_sm[t];
+      // before the first pass overwrites the transform buffer, the bulk store of the previous
+      // pair must have read its staged results out of it
+      auto drained = [&]() {
+        if (store_pending) wait_staged_results_read(t);     // CTA-uniform
+      };
       if (parked) {
         mbar_wait(bar, parity);
         parity ^= 1u;
-        fwd_first_parked<P>(t, w, tb, sm, park, park_len, p.step, store_pending);
+        const bool guard = w.inB + P::N > w.x_len;
+        fwd_first_parked_tm<P>(t, w, sm, park, park_len, p.step, guard, tw_addr, drained);
       } else {
-        if (store_pending) wait_staged_results_read(t);
-        fwd_first<P>(t, w, tb, sm);
+        fwd_first_tm<P>(t, w, sm, tw_addr, drained);
       }
       store_pending = false;
     }
@@ -412,32 +651,26 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
       if (nxt < p.total) {
         SegPair wn;
         pair_of(nxt, wn);
-        parked = parkable(wn);
-        if (parked && t == 0) issue_park(wn);
+        parked = start_park(wn);
       }
     }
-    if constexpr (P::NPASS == 3) {
-      { const TwBases<P> tb = tb_sm[t]; fwd_mid<P>(t, tb, sm); }
-      load_spectrum<P>(t, p.spectrum, hr);
-      __syncwarp();
-      centre<P>(t, hr, sm);
-      __syncwarp();
-      { const TwBases<P> tb = tb_sm[t]; inv_mid<P>(t, tb, sm); }
-    } else {
-      load_spectrum<P>(t, p.spectrum, hr);
-      centre<P>(t, hr, sm);
-    }
+    fwd_mid_tm<P>(t, sm, tw_addr);
+    load_spectrum<P>(t, p.spectrum, hr);
+    __syncwarp();
+    centre<P>(t, hr, sm);
+    __syncwarp();
+    inv_mid_tm<P>(t, sm, tw_addr);
     __syncthreads();
     {
       SegPair w;
       pair_of(item, w);
       float2 v[P::E];
-      { const TwBases<P> tb = tb_sm[t]; inv_last_regs<P>(t, tb, sm, v); }
-      const bool full = !w.accumulate && w.haveB && w.cntA == p.step && w.cntB == p.step;
-      if (full) {
+      inv_last_regs_tm<P>(t, sm, v, tw_addr);
+      if (!w.accumulate) {
         // Results leave through shared memory and one bulk copy per segment (TMA store): the
         // warps do not wait for the stores to drain, the next pair's first pass computes
-        // meanwhile.  stage[phase + tt] keeps shared and global addresses congruent mod 16 B.
+        // meanwhile.  stage[phase + tt] keeps shared and global addresses congruent mod 16 B
+        // (both segments: their outputs start a multiple of 4 floats apart).
         float *st = reinterpret_cast<float *>(sm);
         const int phase = (int)((((unsigned long long)(w.out + w.outA)) >> 2) & 3ull);
         const int span = (p.step + 8 + 3) & ~3;
@@ -445,22 +678,26 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
         __syncthreads();                  // every thread has read its last-pass inputs
         stage_outputs<P>(t, v, w.c_off, p.step, phase, stA, stB);
         __syncthreads();
+        // per segment: `head` scalar samples up to the next 16-byte boundary, a bulk store of
+        // whole 16-byte units, up to 3 scalar samples behind it
         const int head = (4 - phase) & 3;
-        const int mid = (p.step - head) & ~3;
-        const int tail = p.step - head - mid;
         float *ga = w.out + w.outA, *gb = w.out + w.outB;
-        if (t < head) { ga[t] = stA[phase + t]; gb[t] = stB[phase + t]; }
-        if (t >= 32 && t < 32 + tail) {
-          const int k = head + mid + (t - 32);
-          ga[k] = stA[phase + k]; gb[k] = stB[phase + k];
-        }
+        const int midA = w.cntA > head ? (w.cntA - head) & ~3 : 0;
+        const int midB = w.cntB > head ? (w.cntB - head) & ~3 : 0;
+        auto scalar_edges = [&](int u, float *g, const float *stg, int cnt, int mid) {
+          const int k = u < 4 ? u : head + mid + (u - 4);
+          if ((u < 4 ? k < head : true) && k < cnt) g[k] = stg[phase + k];
+        };
+        if (t < 8) scalar_edges(t, ga, stA, w.cntA, midA);
+        else if (t >= 32 && t < 40) scalar_edges(t - 32, gb, stB, w.cntB, midB);
         if (t == 0) {
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          const unsigned bytes = (unsigned)mid * 4u;
-          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(ga + head),
-                       "r"(smem_u32(stA + phase + head)), "r"(bytes) : "memory");
-          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gb + head),
-                       "r"(smem_u32(stB + phase + head)), "r"(bytes) : "memory");
+          if (midA > 0)
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(ga + head),
+                         "r"(smem_u32(stA + phase + head)), "r"((unsigned)midA * 4u) : "memory");
+          if (midB > 0)
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gb + head),
+                         "r"(smem_u32(stB + phase + head)), "r"((unsigned)midB * 4u) : "memory");
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
         store_pending = true;
@@ -471,6 +708,9 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
   }
   // staged results must be out of shared memory before the CTA retires
   if (t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  tmem::fence_before_sync();
+  __syncthreads();
+  if (t < 32) tmem::free_all(*tmem_base);
 }
 
 // ---- plan table ---------------------------------------------------------------------------
@@ -568,14 +808,13 @@ bool launch_persist_16384(OsParams op, const DevJob &job, i64 j0, int taps, cuda
   static bool configured[16] = {false};
   static int sms[16] = {0};
   if (op.total >= 2147483647LL) return false;
-  const size_t smem = sizeof(float2) * PLAN::SMEM_FLOAT2 + sizeof(float) * kParkFloats +
-                      sizeof(fc::TwBases<PLAN>) * PLAN::T + 16;
+  const size_t smem = sizeof(float2) * PLAN::SMEM_FLOAT2 + sizeof(float) * kParkFloats + 16;
+  auto kernel = os_fused_persist_kernel<PLAN>;
   int dev = 0;
   B200_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev >= 16) return false;
   if (!configured[dev]) {
-    B200_CUDA_CHECK(cudaFuncSetAttribute(os_fused_persist_kernel<PLAN>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
     configured[dev] = true;
   }
@@ -591,7 +830,7 @@ bool launch_persist_16384(OsParams op, const DevJob &job, i64 j0, int taps, cuda
   attr[0].val.programmaticStreamSerializationAllowed = after_spectrum ? 1 : 0;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, os_fused_persist_kernel<PLAN>, op));
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, op));
   b200_prof_end(B200_PROF_FUSED, stream);
   b200_count_launch(1);
   return true;
@@ -625,6 +864,9 @@ const float2 *b200_twiddles(int n_fft) {
   float2 *dptr = nullptr;
   B200_CUDA_CHECK(cudaMalloc(&dptr, sizeof(float2) * cnt));
   B200_CUDA_CHECK(cudaMemcpy(dptr, host.data(), sizeof(float2) * cnt, cudaMemcpyHostToDevice));
+  // a copy from pageable memory may return before the DMA has landed, and the kernels that
+  // read the table run on non-blocking streams: wait once, here
+  B200_CUDA_CHECK(cudaDeviceSynchronize());
   g_tw.tab[dev][lg] = dptr;
   return dptr;
 }
@@ -639,7 +881,7 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
   sp.part_taps = part_taps; sp.spectrum = spectrum; sp.tw = tw;
   sp.scale = 1.0f / (float)n_fft;
 
-  OsParams op;
+  OsParams op = {};
   op.x = job.x; op.x_len = job.x_len; op.x_stride = job.x_stride;
   op.out = job.out; op.out_len = job.out_len; op.out_stride = job.out_stride;
   op.tw = tw;
@@ -697,7 +939,7 @@ void b200_os_launch_real(const float2 *tw, float4 *coeffs, int n_fft, const DevJ
   sp.part_taps = (int)job.h_len; sp.spectrum = reinterpret_cast<float2 *>(coeffs); sp.tw = tw;
   sp.scale = 1.0f / (float)n_fft;
 
-  OsParams op;
+  OsParams op = {};
   op.x = job.x; op.x_len = job.x_len; op.x_stride = job.x_stride;
   op.out = job.out; op.out_len = job.out_len; op.out_stride = job.out_stride;
   op.tw = tw;
@@ -801,8 +1043,10 @@ cudaError_t noalloc_setup(int dev, cudaStream_t stream) {
   err = cudaGetLastError();
   if (err != cudaSuccess) return err;
   b200_count_launch(1);
+  err = cudaStreamSynchronize(stream);
+  if (err != cudaSuccess) return err;       // not ready: the next call tries again
   d.ready = true;     // later launches on other streams are ordered by the caller (see header)
-  return cudaStreamSynchronize(stream);
+  return cudaSuccess;
 }
 
 bool noalloc_device_accessible(const void *p) {
@@ -864,6 +1108,8 @@ extern "C" __attribute__((visibility("default"))) int simd_b200_filter_noalloc(
   const NoAllocDevice &d = g_noalloc_dev[dev];
   // every bin of the spectrum array is rewritten by the spectrum kernel of this call, so
   // nothing left over from the previous call is ever read
+  b200_prof_suppress(1);      // simd_b200_profile() would create events
   b200_os_launch_with(d.twiddles + (n / 2 - 128), d.spectrum, n, (int)h_length, job, false, stream);
+  b200_prof_suppress(0);
   return 0;
 }

@@ -186,11 +186,14 @@ struct PeakScratch {       // grow-only per-device scratch, one allocation:
   size_t tiles_cap = 0;
 };
 PeakScratch g_peaks[16];
-std::mutex g_peaks_mu;
+std::recursive_mutex g_peaks_mu;   // recursive: the host-facing call holds it across its two phases
 
 // returns the number of extrema found; writes at most `capacity` of them (device memory)
+// reuse_counts: the tile counts and sums of the previous call (same data, same type, lock held
+// since) are still in the scratch -- go straight to the write pass
 unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_out,
-                             unsigned long long capacity, bool count_only, cudaStream_t stream) {
+                             unsigned long long capacity, bool count_only, cudaStream_t stream,
+                             bool reuse_counts = false) {
   int dev = 0;
   B200_CUDA_CHECK(cudaGetDevice(&dev));
   B200_REQUIRE(dev < 16, "device index out of range");
@@ -199,7 +202,7 @@ unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_ou
   B200_REQUIRE(tiles < 2147483647LL && size < 2147483647LL, "series too long for int positions");
   const int kind = type & 3;            // the reference tests these two bits only
   if (kind == 0) return 0;
-  std::lock_guard<std::mutex> lock(g_peaks_mu);
+  std::lock_guard<std::recursive_mutex> lock(g_peaks_mu);
   PeakScratch &sc = g_peaks[dev];
   if ((size_t)tiles > sc.tiles_cap) {
     if (sc.block_sums) {
@@ -218,11 +221,13 @@ unsigned long long peaks_run(const float *d_data, i64 size, int type, int2 *d_ou
   unsigned *counts = group_sums + sc.tiles_cap / kGroupTiles + 2;
   auto count_kernel = kind == 1 ? peaks_count_kernel<1> : kind == 2 ? peaks_count_kernel<2> : peaks_count_kernel<3>;
   auto write_kernel = kind == 1 ? peaks_write_kernel<1> : kind == 2 ? peaks_write_kernel<2> : peaks_write_kernel<3>;
-  // the tile counts are accumulated atomically: zero them (the sums are plainly written)
-  B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned) * (size_t)tiles, stream));
-  count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, counts);
-  peaks_sums_kernel<<<(unsigned)blocks, kBlockTiles, 0, stream>>>(counts, tiles, group_sums, block_sums);
-  b200_count_launch(2);
+  if (!reuse_counts) {
+    // the tile counts are accumulated atomically: zero them (the sums are plainly written)
+    B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, sizeof(unsigned) * (size_t)tiles, stream));
+    count_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, counts);
+    peaks_sums_kernel<<<(unsigned)blocks, kBlockTiles, 0, stream>>>(counts, tiles, group_sums, block_sums);
+    b200_count_launch(2);
+  }
   if (!count_only) {
     write_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(d_data, size, vec, counts, group_sums, block_sums,
                                                            d_out, capacity);
@@ -270,12 +275,14 @@ extern "C" void b200_detect_peaks(const float *data, long long size, int type, v
     B200_CUDA_CHECK(cudaMemcpyAsync(staged, data, sizeof(float) * (size_t)size, cudaMemcpyHostToDevice, stream));
     d_data = staged;
   }
-  // pass 1: count; then exact-size output, pass 2: write (the count kernels run again inside)
+  // pass 1: count; then an exact-size output; pass 2: the write pass alone, on the counts
+  // pass 1 left in the scratch (the lock keeps other callers off it in between)
+  std::lock_guard<std::recursive_mutex> lock(g_peaks_mu);
   unsigned long long n = peaks_run(d_data, size, type, nullptr, 0, true, stream);
   if (n > 0) {
     int2 *d_out = nullptr;
     B200_CUDA_CHECK(cudaMalloc(&d_out, sizeof(int2) * n));
-    peaks_run(d_data, size, type, d_out, n, false, stream);
+    peaks_run(d_data, size, type, d_out, n, false, stream, true);
     void *host = malloc(sizeof(int2) * n);
     B200_REQUIRE(host, "detect_peaks: out of host memory");
     B200_CUDA_CHECK(cudaMemcpyAsync(host, d_out, sizeof(int2) * n, cudaMemcpyDeviceToHost, stream));

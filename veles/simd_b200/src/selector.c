@@ -114,7 +114,9 @@ ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_
     if (kFusedCost[i].n == n) c = kFusedCost[i].c;
   double fused = fused_cost_us(n, c, (long long)h_length, out_len, (long long)batch);
   if (direct <= fused) return kConvolutionAlgorithmBruteForce;
-  if (x_length > h_length * 2) return kConvolutionAlgorithmOverlapSave;
+  /* the same integer test convolve_overlap_save_initialize asserts (h < x/2, reference
+   * src/convolve.c:105), so that x = 2h+1 goes to the FFT method instead of aborting there */
+  if (x_length / 2 > h_length) return kConvolutionAlgorithmOverlapSave;
   return kConvolutionAlgorithmFFT;
 }
 
