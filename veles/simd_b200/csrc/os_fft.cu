@@ -296,9 +296,6 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned b
       ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
   unsigned ok;
   do {
@@ -352,12 +349,12 @@ __device__ __forceinline__ void tm_twiddle_fwd(float2 *v, unsigned set_addr, tme
 // Forward first pass.  x[inA, inA + park_len) -- zeros where that leaves the signal -- was
 // brought into shared memory (`park`) while the previous pair was being processed: all of
 // segment A and the head of segment B (which starts `step` samples later); the rows of B
-// beyond it come from global memory, bounds-checked when the pair touches the signal's end
-// (`guard`, CTA-uniform).  `before_stores` runs between the arithmetic and the stores into
-// the transform buffer (the previous pair's staged results may still be leaving it).
+// beyond it come from global memory (the caller parks only pairs whose segment B ends inside
+// the signal).  `before_stores` runs between the arithmetic and the stores into the transform
+// buffer (the previous pair's staged results may still be leaving it).
 template <class P, class F>
 __device__ __forceinline__ void fwd_first_parked_tm(int t, const SegPair &w, float2 *sm, const float *park,
-                                                    int park_len, int step, bool guard, unsigned tw_addr,
+                                                    int park_len, int step, unsigned tw_addr,
                                                     F &&before_stores) {
   constexpr int R = P::R1, NB = P::N;
   static_assert(R == 32 && P::E == R, "one radix-32 butterfly per thread");
@@ -370,15 +367,13 @@ __device__ __forceinline__ void fwd_first_parked_tm(int t, const SegPair &w, flo
   tmem::load(a, tw_addr);
   tmem::load(b, tw_addr + 16);
   const float *xb = w.x + (w.inB + base);
-  const i64 left = w.x_len - (w.inB + base);      // samples of the signal from xb on
   const float *pa = park + base;
   static_for<0, R>([&](auto rr) {
     constexpr int r = decltype(rr)::value;
     const float va = pa[r * G::S];
     float vb;
     if (step + (r + 1) * G::S <= park_len) vb = pa[step + r * G::S];   // CTA-uniform
-    else if (!guard) vb = xb[r * G::S];
-    else vb = (i64)(r * G::S) < left ? xb[r * G::S] : 0.0f;
+    else vb = xb[r * G::S];
     v[bitrev(r, ilog2(R))] = make_float2(va, vb);
   });
   dft_inreg<R, false>(v);
@@ -523,9 +518,10 @@ __device__ __forceinline__ void tm_fill_twiddles(int t, const float2 *tw, unsign
 //    left beside the transform buffer, so the next pair's first pass starts from shared
 //    memory instead of waiting for HBM, and the current pair's result stores drain while
 //    that first pass computes.  Needs 16-byte aligned segment starts (the host picks step
-//    and leading-sample count accordingly).  The first and the last pair of a signal stick
-//    out of it: the part of their range that lies outside is zero-filled by the threads, the
-//    part inside is bulk-copied as for every other pair.
+//    and leading-sample count accordingly).  The first pair of a signal starts before it:
+//    that part of the parked range is zero-filled by the threads, the part inside is
+//    bulk-copied as for every other pair.  (A last pair whose segment B runs past the
+//    signal's end takes the bounds-checked loads.)
 //  * Results leave through shared memory and one bulk store per segment.
 constexpr int kParkFloats = 23040;      // 90 KiB beside the 136 KiB transform buffer
 
@@ -572,6 +568,9 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
     int lo, n;
     park_span(w, lo, n);
     if (n <= 0) return false;                           // CTA-uniform
+    // rows of B behind the parked range are read from global memory without bounds checks
+    // (a per-row check in the hot first pass measured 2.4 % on C4)
+    if (need > park_len && w.inB + P::N > w.x_len) return false;
     if (lo > 0 || lo + n < park_len) {
       // a signal edge: zeros in front of the signal, zeros (and up to 3 samples the 16-byte
       // granularity left over) behind it
@@ -636,8 +635,7 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
       if (parked) {
         mbar_wait(bar, parity);
         parity ^= 1u;
-        const bool guard = w.inB + P::N > w.x_len;
-        fwd_first_parked_tm<P>(t, w, sm, park, park_len, p.step, guard, tw_addr, drained);
+        fwd_first_parked_tm<P>(t, w, sm, park, park_len, p.step, tw_addr, drained);
       } else {
         fwd_first_tm<P>(t, w, sm, tw_addr, drained);
       }
