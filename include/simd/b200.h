@@ -14,6 +14,8 @@
 #include <simd/common.h>
 #include <simd/attributes.h>
 #include <simd/convolve_structs.h>
+#include <simd/detect_peaks.h>
+#include <stdint.h>
 
 SIMD_API_BEGIN
 
@@ -30,6 +32,34 @@ void cross_correlate_batch(struct ConvolutionHandle handle, const float *x, size
                            const float *h, float *result, size_t result_stride,
                            size_t batch) NOTNULL(2, 4, 5);
 
+/* ---- fewer bytes over PCIe for host-pointer callers -----------------------------------
+ * A drop-in caller hands over host memory, and end to end such a call is bound by the host
+ * link, not by the kernels (BENCH: ~45 GB/s each way against ~2.3 TB/s of kernel traffic).
+ * Two chains of the reference API that a caller would otherwise run as separate calls are
+ * offered as one, so that the bulky intermediate never crosses the link:
+ *
+ * int16 samples (PCM, ADC data): the reference widens them on the host with int16_to_float
+ * (inc/simd/arithmetic.h:231-278) and convolves the floats.  Here the int16 samples are
+ * what is copied to the GPU (2 bytes per sample instead of 4) and they are widened there,
+ * inside the staging pipeline.  x: HOST memory, x_stride in samples; everything else as
+ * convolve_batch / cross_correlate_batch; the result is what the float call gives on
+ * (float)x[i]. */
+void convolve_batch_int16(struct ConvolutionHandle handle, const int16_t *x, size_t x_stride,
+                          const float *h, float *result, size_t result_stride, size_t batch)
+    NOTNULL(2, 4, 5);
+void cross_correlate_batch_int16(struct ConvolutionHandle handle, const int16_t *x,
+                                 size_t x_stride, const float *h, float *result,
+                                 size_t result_stride, size_t batch) NOTNULL(2, 4, 5);
+
+/* cross_correlate() followed by detect_peaks() (reference src/correlate.c:144-156, then
+ * src/detect_peaks.c:58-127) with the x_length+h_length-1 correlation samples kept in GPU
+ * memory: only the extrema travel back.  *results as detect_peaks() returns it (malloc()ed,
+ * NULL when there is none). */
+void simd_b200_cross_correlate_peaks(struct ConvolutionHandle handle, const float *x,
+                                     const float *h, ExtremumType type,
+                                     ExtremumPoint **results, size_t *resultsLength)
+    NOTNULL(2, 3, 5, 6);
+
 /* ---- shard primitive ------------------------------------------------------------------
  * Filters a piece of a longer signal:
  *   result[n] = sum_j g[j] * X(n + j - left_pad),  n in [0, result_length)
@@ -42,6 +72,40 @@ void cross_correlate_batch(struct ConvolutionHandle handle, const float *x, size
 void simd_b200_filter_shard(const float *x, size_t x_length, const float *h,
                             size_t h_length, int reverse, size_t left_pad, float *result,
                             size_t result_length, int algorithm) NOTNULL(1, 3, 7);
+
+/* ---- several GPUs from one process ----------------------------------------------------
+ * The reference is single-threaded and knows one address space.  A host-pointer caller of
+ * the batched calls, or of simd_b200_filter_long, can let the library spread the work over
+ * the GPUs of the box: one host thread, one set of staging buffers and one PCIe link per
+ * device; batches split by rows, a long signal by contiguous output ranges whose (h-1)
+ * samples of halo are read from the caller's buffer.  No collective, no peer traffic.
+ *   simd_b200_use_devices(n)   n GPUs from now on, starting at the calling thread's current
+ *                              device (0 = all visible).  Default 1: nothing changes for a
+ *                              program that manages devices itself.
+ * Device-pointer calls always run on the current device. */
+void simd_b200_use_devices(int n);
+int simd_b200_devices_in_use(void);
+
+/* Full convolution (reverse = 0) or cross-correlation (reverse != 0) of one long signal:
+ * result[0 .. x_length+h_length-2], as convolve() / cross_correlate() on a handle made for
+ * these lengths (reference src/convolve.c:381-395), without a handle and over
+ * simd_b200_devices_in_use() GPUs when the pointers are host memory. */
+void simd_b200_filter_long(const float *x, size_t x_length, const float *h, size_t h_length,
+                           int reverse, float *result) NOTNULL(1, 3, 6);
+
+/* The same operation on a signal that already lives sharded in the memories of several GPUs
+ * (one process, all devices visible).  Shard i = samples [s_i, e_i) of the signal, at
+ * x_shards[i] on device devices[i], with h_length-1 writable floats in FRONT of it: the call
+ * copies the tail of shard i-1 there (cudaMemcpyPeerAsync over NVLink; the halo lands in
+ * local memory before the kernels of that GPU start -- no kernel reads a peer's memory), then
+ * every GPU filters its shard.  result_shards[i] receives shard_lengths[i] samples of the
+ * result, the last one h_length-1 more; concatenated they are the full result.
+ * h_on_device[i] is a copy of h in device i's memory.  Every shard but the last must hold at
+ * least h_length-1 samples.  Returns after all GPUs have finished. */
+void simd_b200_filter_long_sharded(int n_shards, const int *devices, float *const *x_shards,
+                                   const size_t *shard_lengths, const float *const *h_on_device,
+                                   size_t h_length, int reverse, float *const *result_shards)
+    NOTNULL(2, 3, 4, 5, 8);
 
 /* ---- selector, exposed for inspection and tests (pure host logic, no CUDA call) -------
  * The decision convolve_initialize makes on B200 (replaces the 2h / 200 / 350 rules of

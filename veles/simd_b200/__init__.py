@@ -94,8 +94,23 @@ def _load():
         b = getattr(L, p + "_batch")
         b.argtypes = [ConvolutionHandle, vp, sz, vp, vp, sz, sz]
         b.restype = None
+    for p in ("convolve", "cross_correlate"):
+        b = getattr(L, p + "_batch_int16")
+        b.argtypes = [ConvolutionHandle, vp, sz, vp, vp, sz, sz]
+        b.restype = None
+    L.simd_b200_cross_correlate_peaks.argtypes = [ConvolutionHandle, vp, vp, C.c_int,
+                                                  C.POINTER(C.POINTER(ExtremumPoint)), C.POINTER(sz)]
+    L.simd_b200_cross_correlate_peaks.restype = None
     L.simd_b200_filter_shard.argtypes = [vp, sz, vp, sz, C.c_int, sz, vp, sz, C.c_int]
     L.simd_b200_filter_shard.restype = None
+    L.simd_b200_use_devices.argtypes = [C.c_int]
+    L.simd_b200_use_devices.restype = None
+    L.simd_b200_devices_in_use.restype = C.c_int
+    L.simd_b200_filter_long.argtypes = [vp, sz, vp, sz, C.c_int, vp]
+    L.simd_b200_filter_long.restype = None
+    L.simd_b200_filter_long_sharded.argtypes = [C.c_int, C.POINTER(C.c_int), C.POINTER(vp), C.POINTER(sz),
+                                                C.POINTER(vp), sz, C.c_int, C.POINTER(vp)]
+    L.simd_b200_filter_long_sharded.restype = None
     L.simd_b200_select_algorithm.argtypes = [sz, sz]
     L.simd_b200_select_algorithm.restype = C.c_int
     L.simd_b200_select_algorithm_batch.argtypes = [sz, sz, sz]
@@ -166,7 +181,9 @@ EXPORTED_SYMBOLS = (
     "cross_correlate_overlap_save_finalize cross_correlate_initialize cross_correlate "
     "cross_correlate_finalize mallocf malloc_aligned memsetf rmemcpyf convolve_batch "
     "cross_correlate_batch simd_b200_filter_shard simd_b200_select_algorithm "
-    "simd_b200_select_algorithm_batch "
+    "simd_b200_select_algorithm_batch simd_b200_use_devices simd_b200_devices_in_use "
+    "simd_b200_filter_long simd_b200_filter_long_sharded convolve_batch_int16 "
+    "cross_correlate_batch_int16 simd_b200_cross_correlate_peaks "
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
     "simd_b200_synchronize simd_b200_device_count simd_b200_kernel_launches "
     "simd_b200_profile simd_b200_profile_collect simd_b200_filter_noalloc "
@@ -428,3 +445,76 @@ def filter_shard(x, h, reverse, left_pad, result_length, algorithm=-1, out=None)
     lib.simd_b200_filter_shard(_ptr(x), x.shape[-1], _ptr(h), h.shape[-1], int(reverse),
                                int(left_pad), _ptr(out), int(result_length), int(algorithm))
     return out
+
+
+def batch_int16(handle, x16, h, out=None):
+    """convolve_batch_int16 / cross_correlate_batch_int16: x16 is a host int16 array (batch, x_len)
+    (numpy, or a pinned torch tensor); h and out are float32."""
+    assert handle.kind == ""
+    if _is_torch(x16):
+        assert x16.dtype.itemsize == 2 and not x16.is_cuda and x16.stride(-1) == 1
+        xp, xs, nb = x16.data_ptr(), x16.stride(0), x16.shape[0]
+    else:
+        x16 = np.ascontiguousarray(x16, dtype=np.int16)
+        xp, xs, nb = x16.ctypes.data, x16.strides[0] // 2, x16.shape[0]
+    olen = handle.x_length + handle.h_length - 1
+    if out is None:
+        out = np.empty((nb, olen), dtype=np.float32)
+    os_ = out.stride(0) if _is_torch(out) else out.strides[0] // 4
+    if not _is_torch(h):
+        h = np.ascontiguousarray(h, dtype=np.float32)
+    getattr(lib, handle.prefix + "_batch_int16")(handle.handle, xp, xs, _ptr(h), _ptr(out), os_, nb)
+    return out
+
+
+def cross_correlate_peaks(x, h, type_=EXTREMUM_BOTH):
+    """simd_b200_cross_correlate_peaks: (positions, values) of the extrema of x (x) h; the
+    correlation itself stays on the GPU."""
+    x, h = _prep(x, h)
+    res = C.POINTER(ExtremumPoint)()
+    n = C.c_size_t(0)
+    with Handle(x.shape[-1], h.shape[-1], "", True) as hd:
+        lib.simd_b200_cross_correlate_peaks(hd.handle, _ptr(x), _ptr(h), int(type_), C.byref(res), C.byref(n))
+    if n.value == 0:
+        return np.empty(0, np.int32), np.empty(0, np.float32)
+    raw = np.ctypeslib.as_array(C.cast(res, C.POINTER(C.c_int32)), shape=(n.value, 2)).copy()
+    C.CDLL(None).free(res)
+    return raw[:, 0].copy(), raw[:, 1].copy().view(np.float32)
+
+
+def use_devices(n):
+    """simd_b200_use_devices: host-pointer batches / long signals spread over n GPUs (0 = all)."""
+    lib.simd_b200_use_devices(int(n))
+    return lib.simd_b200_devices_in_use()
+
+
+def filter_long(x, h, reverse=False, out=None):
+    """simd_b200_filter_long: full convolution / correlation of one long signal (host arrays
+    are spread over the GPUs chosen with use_devices)."""
+    x, h = _prep(x, h)
+    if out is None:
+        out = _empty_like(x, (x.shape[-1] + h.shape[-1] - 1,))
+    lib.simd_b200_filter_long(_ptr(x), x.shape[-1], _ptr(h), h.shape[-1], int(bool(reverse)), _ptr(out))
+    return out
+
+
+def filter_long_sharded(x_shards, h_copies, reverse=False, results=None):
+    """simd_b200_filter_long_sharded over torch CUDA tensors, one shard per device.  Every
+    x_shards[i] must be a view that has h-1 elements of storage in front of it (see
+    sharded.alloc_shard); h_copies[i] is h on x_shards[i]'s device."""
+    import torch
+    n = len(x_shards)
+    hl = h_copies[0].numel()
+    if results is None:
+        results = [torch.empty(x.numel() + (hl - 1 if i == n - 1 else 0), device=x.device)
+                   for i, x in enumerate(x_shards)]
+    for x in x_shards:                     # each device's library stream follows torch's
+        with torch.cuda.device(x.device):
+            _follow_torch_stream(x.device.index)
+    devs = (C.c_int * n)(*[x.device.index for x in x_shards])
+    xs = (C.c_void_p * n)(*[x.data_ptr() for x in x_shards])
+    lens = (C.c_size_t * n)(*[x.numel() for x in x_shards])
+    hs = (C.c_void_p * n)(*[h.data_ptr() for h in h_copies])
+    rs = (C.c_void_p * n)(*[r.data_ptr() for r in results])
+    lib.simd_b200_filter_long_sharded(n, devs, xs, lens, hs, hl, int(bool(reverse)), rs)
+    return results

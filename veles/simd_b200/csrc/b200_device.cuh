@@ -64,6 +64,9 @@ void b200_os_launch_with(const float2 *twiddles, float2 *spectrum, int n_fft, in
 void b200_os_launch_real(const float2 *twiddles, float4 *coeffs, int n_fft, const DevJob &job,
                          cudaStream_t stream);
 
+// convert.cu: device-to-device int16 -> float on a given stream (staging of int16 input)
+void b200_int16_to_float_on(const short *d_in, i64 n, float *d_out, cudaStream_t stream);
+
 void b200_count_launch(int n);
 
 // Optional per-kernel CUDA-event timing (simd_b200_profile): kind 0 = direct kernel,

@@ -30,6 +30,8 @@ typedef struct B200Job {
   long long pad;
   long long batch;
   int reverse;
+  int x_int16;   /* x points at int16_t samples in HOST memory (strides and lengths still count
+                  * samples): they cross PCIe as 2 bytes each and are widened on the device */
 } B200Job;
 
 /* Algorithms; numeric values follow ConvolutionAlgorithm (convolve_structs.h). */
@@ -43,6 +45,8 @@ typedef struct B200Plan B200Plan;   /* opaque; lives behind handle.fft_plan */
 B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len, int n_fft,
                            int real_packed);
 void b200_plan_destroy(B200Plan *plan);
+float *b200_device_alloc(size_t floats);           /* cudaMalloc / cudaFree on the current device */
+void b200_device_free(float *p);
 float *b200_plan_spectrum(const B200Plan *plan);   /* device pointer */
 float *b200_plan_scratch(const B200Plan *plan);    /* device pointer */
 
@@ -50,6 +54,16 @@ float *b200_plan_scratch(const B200Plan *plan);    /* device pointer */
  * device buffers and the call returns after the result is back in host memory; device
  * pointers are used in place and the call is asynchronous on the library stream. */
 void b200_run(B200Plan *plan, int algorithm, const B200Job *job);
+
+/* Several GPUs from one process (csrc/context.cu).  b200_use_devices(n): host-pointer jobs
+ * given to b200_run_multi are spread over n GPUs (0 = all visible; default 1). */
+void b200_use_devices(int n);
+int b200_devices_in_use(void);
+void b200_run_multi(B200Plan *plan, int algorithm, const B200Job *job);
+void b200_filter_long_sharded(int n_shards, const int *devices, float *const *x_shards,
+                              const size_t *shard_lengths, const float *const *h_on_device,
+                              size_t h_len, int reverse, float *const *result_shards,
+                              int algorithm);
 
 /* transform-length policy (src/selector.c, pure host logic) */
 int b200_os_pick_n(long long h_len, long long out_len);

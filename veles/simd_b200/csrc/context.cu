@@ -10,6 +10,7 @@
 #include <atomic>
 #include <mutex>
 #include <string.h>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -19,6 +20,8 @@ constexpr int kMaxDev = 16;
 struct Staging {        // grow-only device staging for host-pointer callers (two slots)
   float *x[2] = {nullptr, nullptr}, *out[2] = {nullptr, nullptr}, *h = nullptr;
   size_t x_cap[2] = {0, 0}, out_cap[2] = {0, 0}, h_cap = 0;
+  float *x16[2] = {nullptr, nullptr};      // int16 samples as they arrive (2 B each), before
+  size_t x16_cap[2] = {0, 0};              // the on-device conversion; capacity in floats
 };
 
 struct Pipe {           // copy streams / events of the host-pointer pipeline
@@ -27,8 +30,18 @@ struct Pipe {           // copy streams / events of the host-pointer pipeline
   cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
 };
 
+// Host-pointer calls too small for the pipeline below to pay (a reference-API caller hands
+// over a few KB per call): one pinned, device-mapped bounce buffer per device.
+struct SmallPipe {
+  float *pin = nullptr;                // cudaHostAlloc(Mapped): [x | h | result]
+  size_t cap = 0;                      // floats
+  std::mutex mu;
+};
+constexpr long long kSmallJobFloats = 64 * 1024;   // x + h + result of one call (256 KiB)
+
 struct DeviceCtx {
   cudaStream_t own_stream = nullptr;   // created lazily, non-blocking
+  SmallPipe small;
   Staging staging;                     // used by handle-less calls (convolve_simd, ...)
   Pipe pipe;
   float2 *spectrum = nullptr;          // scratch for handle-less FFT jobs
@@ -36,6 +49,7 @@ struct DeviceCtx {
 };
 
 std::mutex g_mu;                 // guards contexts, the shared staging and user stream
+std::mutex g_staged_call_mu;     // handle-less host-pointer calls share the per-device staging
 DeviceCtx g_ctx[kMaxDev];
 std::atomic<void *> g_user_stream[kMaxDev];       // per device: a stream belongs to one device
 std::atomic<int> g_have_user_stream[kMaxDev];
@@ -89,9 +103,14 @@ struct B200Plan {
   int algorithm;
   int device;
   i64 x_len, h_len;
+  int real_packed_arg;
   OsDevPlan os;
   Staging staging;
   std::mutex mu;       // one thread per handle at a time (reference: shared scratch)
+  // the same plan on the other GPUs of the box, created on first use by the multi-GPU calls
+  // (simd_b200_use_devices) and destroyed with this one
+  B200Plan *peer[kMaxDev] = {};
+  std::mutex peer_mu;
 };
 
 void b200_count_launch(int n) { g_launches.fetch_add(n); }
@@ -175,6 +194,7 @@ extern "C" B200Plan *b200_plan_create(int algorithm, long long x_len, long long 
   plan->device = current_device();
   plan->x_len = x_len;
   plan->h_len = h_len;
+  plan->real_packed_arg = real_packed;
   B200_REQUIRE(n_fft >= B200_FFT_MIN && n_fft <= B200_FFT_MAX && (n_fft & (n_fft - 1)) == 0,
                "transform length must be a power of two in range");
   plan->os.n_fft = n_fft;
@@ -203,6 +223,9 @@ extern "C" B200Plan *b200_plan_create(int algorithm, long long x_len, long long 
 extern "C" void b200_plan_destroy(B200Plan *plan) {
   if (!plan) return;
   B200_REQUIRE(plan->magic == 0xB200, "not a libSimd(b200) plan");
+  for (int d = 0; d < kMaxDev; d++) {
+    if (plan->peer[d]) { b200_plan_destroy(plan->peer[d]); plan->peer[d] = nullptr; }
+  }
   int prev = current_device();
   if (prev != plan->device) B200_CUDA_CHECK(cudaSetDevice(plan->device));
   // outstanding asynchronous work may still read the spectrum / staging buffers
@@ -211,11 +234,22 @@ extern "C" void b200_plan_destroy(B200Plan *plan) {
   for (int sl = 0; sl < 2; sl++) {
     cudaFree(plan->staging.x[sl]);
     cudaFree(plan->staging.out[sl]);
+    cudaFree(plan->staging.x16[sl]);
   }
   cudaFree(plan->staging.h);
   if (prev != plan->device) B200_CUDA_CHECK(cudaSetDevice(prev));
   plan->magic = 0;
   delete plan;
+}
+
+// plain device buffers for the host layer (cross-correlate -> peaks keeps its result here)
+extern "C" float *b200_device_alloc(size_t floats) {
+  float *p = nullptr;
+  B200_CUDA_CHECK(cudaMalloc(&p, sizeof(float) * (floats ? floats : 1)));
+  return p;
+}
+extern "C" void b200_device_free(float *p) {
+  if (p) B200_CUDA_CHECK(cudaFree(p));
 }
 
 extern "C" float *b200_plan_spectrum(const B200Plan *plan) { return (float *)plan->os.spectrum; }
@@ -285,6 +319,52 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     return;
   }
 
+  // ---- small host-pointer jobs --------------------------------------------------------
+  // One memcpy into a pinned bounce buffer, one stream, no events, one synchronise:
+  //   direct kernel   the kernel reads x / h from and writes the result to the bounce buffer
+  //                   itself (mapped host memory: one launch, no copy commands at all)
+  //   transform path  one H2D copy of [x | h], the two kernels, one D2H copy of the result
+  // This is the path a drop-in caller of convolve() / convolve_simd() with the reference's
+  // test shapes takes (tests/convolve.cc:139-166: x = 1024, h = 50).
+  B200_REQUIRE(!(job->x_int16 && xd), "int16 samples are converted while they are staged: pass host memory");
+  if (!xd && !hd && !od && job->batch == 1 && !job->x_int16 &&
+      job->x_len + job->h_len + job->out_len <= kSmallJobFloats) {
+    SmallPipe &sp = g_ctx[dev].small;
+    std::unique_lock<std::mutex> plan_lock;
+    if (plan) plan_lock = std::unique_lock<std::mutex>(plan->mu);
+    std::lock_guard<std::mutex> lock(sp.mu);
+    // 64-float (256-byte) aligned sections: wide loads and bulk copies stay legal
+    const size_t xo = 0, ho = ((size_t)job->x_len + 63) & ~(size_t)63;
+    const size_t oo = ho + (((size_t)job->h_len + 63) & ~(size_t)63);
+    const size_t total = oo + (size_t)job->out_len;
+    if (total > sp.cap) {
+      if (sp.pin) { B200_CUDA_CHECK(cudaStreamSynchronize(stream)); B200_CUDA_CHECK(cudaFreeHost(sp.pin)); }
+      sp.cap = (size_t)kSmallJobFloats + 256;
+      B200_CUDA_CHECK(cudaHostAlloc(&sp.pin, sp.cap * sizeof(float), cudaHostAllocMapped));
+    }
+    memcpy(sp.pin + xo, job->x, sizeof(float) * (size_t)job->x_len);
+    memcpy(sp.pin + ho, job->h, sizeof(float) * (size_t)job->h_len);
+    if (algorithm == B200_ALG_DIRECT) {
+      dj.x = sp.pin + xo; dj.h = sp.pin + ho; dj.out = sp.pin + oo;
+      launch_device_job(plan, algorithm, dj, stream);
+    } else {
+      std::unique_lock<std::mutex> ctx_lock;
+      if (!plan) ctx_lock = std::unique_lock<std::mutex>(g_staged_call_mu);
+      Staging *st = plan ? &plan->staging : &g_ctx[dev].staging;
+      grow(&st->x[0], &st->x_cap[0], oo + (size_t)job->h_len);   // [x | h] in one piece
+      grow(&st->out[0], &st->out_cap[0], (size_t)job->out_len);
+      B200_CUDA_CHECK(cudaMemcpyAsync(st->x[0], sp.pin, sizeof(float) * (ho + (size_t)job->h_len),
+                                      cudaMemcpyHostToDevice, stream));
+      dj.x = st->x[0] + xo; dj.h = st->x[0] + ho; dj.out = st->out[0];
+      launch_device_job(plan, algorithm, dj, stream);
+      B200_CUDA_CHECK(cudaMemcpyAsync(sp.pin + oo, st->out[0], sizeof(float) * (size_t)job->out_len,
+                                      cudaMemcpyDeviceToHost, stream));
+    }
+    B200_CUDA_CHECK(cudaStreamSynchronize(stream));
+    memcpy(job->out, sp.pin + oo, sizeof(float) * (size_t)job->out_len);
+    return;
+  }
+
   // ---- host-pointer path: stage, run, copy back, synchronise --------------------------
   // The job is cut into pieces (groups of whole signals, or -- for one long signal -- time
   // slices with their (h-1)-sample halo) that flow through two staging slots on three
@@ -297,8 +377,7 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     st = &plan->staging;
   } else {
     // handle-less calls share the per-device staging: serialise them
-    static std::mutex staged_call_mu;
-    ctx_lock = std::unique_lock<std::mutex>(staged_call_mu);
+    ctx_lock = std::unique_lock<std::mutex>(g_staged_call_mu);
     st = &g_ctx[dev].staging;
   }
   // the copy streams and events are one set per device: host-pointer calls of different
@@ -348,6 +427,7 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
                                   : (job->batch + rows_per_piece - 1) / rows_per_piece;
   for (int sl = 0; sl < (n_pieces > 1 ? 2 : 1); sl++) {
     if (!xd) grow(&st->x[sl], &st->x_cap[sl], (size_t)piece_x);
+    if (job->x_int16) grow(&st->x16[sl], &st->x16_cap[sl], ((size_t)piece_x + 1) / 2);
     if (!od) grow(&st->out[sl], &st->out_cap[sl], (size_t)piece_o);
   }
   if (!hd) {
@@ -361,6 +441,7 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     const int sl = (int)(pi & 1);
     // --- describe the piece ---------------------------------------------------------------
     const float *src_x; float *dst_o;
+    i64 x_off;                       // first sample of the piece, in samples from job->x
     i64 px_len, po_len, p_rows, p_pad;
     if (slice_time) {
       const i64 o0 = pi * outs_per_piece;
@@ -368,19 +449,34 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
       i64 lo = o0 - job->pad; if (lo < 0) lo = 0;
       i64 hi = o1 - job->pad + job->h_len - 1; if (hi > x_row) hi = x_row;
       if (hi < lo) hi = lo;
-      src_x = job->x + lo; px_len = hi - lo; p_pad = job->pad - o0 + lo;
+      x_off = lo; px_len = hi - lo; p_pad = job->pad - o0 + lo;
       dst_o = job->out + o0; po_len = o1 - o0; p_rows = 1;
     } else {
       const i64 b0 = pi * rows_per_piece;
       p_rows = (job->batch - b0) < rows_per_piece ? (job->batch - b0) : rows_per_piece;
-      src_x = job->x + b0 * job->x_stride; px_len = x_row; p_pad = job->pad;
+      x_off = b0 * job->x_stride; px_len = x_row; p_pad = job->pad;
       dst_o = job->out + b0 * job->out_stride; po_len = o_row;
     }
+    src_x = job->x_int16 ? nullptr : job->x + x_off;
     dj.batch = p_rows; dj.x_len = px_len; dj.out_len = po_len; dj.pad = p_pad;
     // --- H2D ------------------------------------------------------------------------------
     if (!xd) {
       if (pi >= 2) B200_CUDA_CHECK(cudaStreamWaitEvent(pipe.s_in, pipe.ev_comp[sl], 0));
-      if (px_len > 0) {
+      if (px_len > 0 && job->x_int16) {
+        // 2 bytes per sample over PCIe; widened to float on the device, into the slot the
+        // kernels read (reference converter: inc/simd/arithmetic.h:231-278)
+        const short *src16 = reinterpret_cast<const short *>(job->x) + x_off;
+        short *dst16 = reinterpret_cast<short *>(st->x16[sl]);
+        if (p_rows == 1 || job->x_stride == px_len) {
+          B200_CUDA_CHECK(cudaMemcpyAsync(dst16, src16, sizeof(short) * px_len * p_rows,
+                                          cudaMemcpyHostToDevice, pipe.s_in));
+        } else {
+          B200_CUDA_CHECK(cudaMemcpy2DAsync(dst16, sizeof(short) * px_len, src16,
+                                            sizeof(short) * job->x_stride, sizeof(short) * px_len,
+                                            (size_t)p_rows, cudaMemcpyHostToDevice, pipe.s_in));
+        }
+        b200_int16_to_float_on(dst16, px_len * p_rows, st->x[sl], pipe.s_in);
+      } else if (px_len > 0) {
         if (p_rows == 1 || job->x_stride == px_len) {   // contiguous: no 2-D pitch limit
           B200_CUDA_CHECK(cudaMemcpyAsync(st->x[sl], src_x, sizeof(float) * px_len * p_rows,
                                           cudaMemcpyHostToDevice, pipe.s_in));
@@ -425,4 +521,137 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
   }
   if (!od) B200_CUDA_CHECK(cudaStreamSynchronize(pipe.s_out));
   B200_CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+
+
+// ---- several GPUs from one process ---------------------------------------------------------
+// The reference has no parallelism on this path (src/convolve.c:179-180 declines even OpenMP);
+// north_star: batches of independent signals, and long signals cut into pieces with an
+// (h-1)-sample halo, partition across the GPUs of one box with no collective.  A host-pointer
+// job is cut into one slice per device -- groups of whole signals, or for a single long signal
+// contiguous output ranges, each reading its own (h-1)-sample halo straight from the caller's
+// host buffer -- and every slice runs through the single-GPU path above (b200_run) on its own
+// device from its own host thread: own staging buffers, own copy streams, own PCIe link.
+
+namespace {
+std::atomic<int> g_use_devices{1};
+
+B200Plan *plan_on_device(B200Plan *plan, int dev) {
+  if (!plan || plan->device == dev) return plan;
+  std::lock_guard<std::mutex> lock(plan->peer_mu);
+  if (!plan->peer[dev]) {
+    // current device is `dev` (the worker thread selected it)
+    plan->peer[dev] = b200_plan_create(plan->algorithm, plan->x_len, plan->h_len, plan->os.n_fft,
+                                       plan->real_packed_arg);
+  }
+  return plan->peer[dev];
+}
+}  // namespace
+
+extern "C" void b200_use_devices(int n) {
+  int have = b200_device_count();
+  // test knob: VELES_B200_OVERSUBSCRIBE=1 lets n exceed the GPUs present (slices then share
+  // devices round-robin), so the partitioning can be exercised on a one-GPU box
+  if (n <= 0 || (n > have && !getenv("VELES_B200_OVERSUBSCRIBE"))) n = have;
+  if (n > kMaxDev) n = kMaxDev;
+  g_use_devices.store(n < 1 ? 1 : n);
+}
+extern "C" int b200_devices_in_use(void) { return g_use_devices.load(); }
+
+extern "C" void b200_run_multi(B200Plan *plan, int algorithm, const B200Job *job) {
+  const int ndev = g_use_devices.load();
+  const bool host_job = !is_device_pointer(job->x);      // the bulk of the traffic is host memory
+  // slices worth a thread and a pipeline each: at least 2^20 outputs per device
+  const i64 work = job->batch * job->out_len;
+  int parts = ndev;
+  if (work / ((i64)1 << 20) < parts) parts = (int)(work / ((i64)1 << 20));
+  if (job->batch > 1 && job->batch < parts) parts = (int)job->batch;
+  if (!host_job || parts <= 1) {
+    b200_run(plan, algorithm, job);
+    return;
+  }
+  const int dev0 = current_device();
+  const int have = b200_device_count();
+  std::vector<std::thread> workers;
+  for (int i = 0; i < parts; i++) {
+    B200Job sj = *job;
+    if (job->batch > 1) {
+      const i64 base = job->batch / parts, rem = job->batch % parts;
+      const i64 b0 = i * base + (i < rem ? i : rem);
+      sj.batch = base + (i < rem ? 1 : 0);
+      sj.x = job->x_int16 ? reinterpret_cast<const float *>(reinterpret_cast<const short *>(job->x) + b0 * job->x_stride)
+                          : job->x + b0 * job->x_stride;
+      sj.out = job->out + b0 * job->out_stride;
+    } else {
+      // contiguous output range [o0, o1) of one long signal; the samples it needs are
+      // x[o0 - pad, o1 - pad + h - 1), clipped to the signal
+      const i64 per = (job->out_len + parts - 1) / parts;
+      const i64 o0 = i * per;
+      const i64 o1 = o0 + per < job->out_len ? o0 + per : job->out_len;
+      if (o1 <= o0) continue;
+      i64 lo = o0 - job->pad; if (lo < 0) lo = 0;
+      i64 hi = o1 - job->pad + job->h_len - 1; if (hi > job->x_len) hi = job->x_len;
+      if (hi < lo) hi = lo;
+      if (hi == lo) {       // nothing of the signal under this range: zeros
+        memset(job->out + o0, 0, sizeof(float) * (size_t)(o1 - o0));
+        continue;
+      }
+      sj.x = job->x_int16 ? reinterpret_cast<const float *>(reinterpret_cast<const short *>(job->x) + lo) : job->x + lo;
+      sj.x_len = hi - lo; sj.x_stride = sj.x_len;
+      sj.pad = job->pad - o0 + lo;
+      sj.out = job->out + o0; sj.out_len = o1 - o0; sj.out_stride = sj.out_len;
+    }
+    const int dev = (dev0 + i) % have;
+    workers.emplace_back([plan, algorithm, sj, dev]() {
+      B200_CUDA_CHECK(cudaSetDevice(dev));
+      // a long signal's slices have other lengths than the handle was made for: they run
+      // without it (context-owned scratch, the same kernels)
+      B200Plan *mine = sj.x_len == (plan ? plan->x_len : sj.x_len) ? plan_on_device(plan, dev) : nullptr;
+      b200_run(mine, algorithm, &sj);
+    });
+  }
+  for (std::thread &w : workers) w.join();
+  B200_CUDA_CHECK(cudaSetDevice(dev0));
+}
+
+// Device-resident shards of one long signal, one per GPU: shard i holds x[s_i, e_i) at
+// x_shards[i] with h_len-1 writable floats in front of it.  Each shard's tail is copied into
+// the front of its right neighbour (cudaMemcpyPeerAsync on the neighbour's stream: the halo
+// lands in local memory before the unchanged single-GPU kernels run; no kernel reads a peer's
+// memory), then every GPU filters [halo | shard] with pad = 0 (shard 0: pad = h_len-1, its
+// halo is the implicit zeros).  The last shard also produces the h_len-1 tail outputs.
+extern "C" void b200_filter_long_sharded(int n_shards, const int *devices, float *const *x_shards,
+                                         const size_t *shard_lengths, const float *const *h_on_device,
+                                         size_t h_len, int reverse, float *const *result_shards,
+                                         int algorithm) {
+  B200_REQUIRE(n_shards >= 1 && devices && x_shards && shard_lengths && h_on_device && result_shards,
+               "filter_long_sharded: null argument");
+  const int dev0 = current_device();
+  const i64 halo = (i64)h_len - 1;
+  for (int i = 0; i < n_shards; i++) {
+    B200_REQUIRE(shard_lengths[i] > 0 && (i == 0 || (i64)shard_lengths[i - 1] >= halo),
+                 "filter_long_sharded: a shard is shorter than the h-1 halo its neighbour needs");
+    B200_CUDA_CHECK(cudaSetDevice(devices[i]));
+    cudaStream_t stream = current_stream();
+    B200Job sj = {};
+    sj.h = h_on_device[i]; sj.h_len = (i64)h_len; sj.reverse = reverse; sj.batch = 1;
+    sj.out = result_shards[i];
+    sj.out_len = (i64)shard_lengths[i] + (i == n_shards - 1 ? halo : 0);
+    sj.out_stride = sj.out_len;
+    if (i == 0 || halo == 0) {
+      sj.x = x_shards[i]; sj.x_len = (i64)shard_lengths[i]; sj.pad = i == 0 ? halo : 0;
+    } else {
+      B200_CUDA_CHECK(cudaMemcpyPeerAsync(x_shards[i] - halo, devices[i],
+                                          x_shards[i - 1] + shard_lengths[i - 1] - halo, devices[i - 1],
+                                          sizeof(float) * (size_t)halo, stream));
+      sj.x = x_shards[i] - halo; sj.x_len = (i64)shard_lengths[i] + halo; sj.pad = 0;
+    }
+    sj.x_stride = sj.x_len;
+    b200_run(nullptr, algorithm, &sj);       // no handle: the device context's scratch
+  }
+  for (int i = 0; i < n_shards; i++) {
+    B200_CUDA_CHECK(cudaSetDevice(devices[i]));
+    B200_CUDA_CHECK(cudaStreamSynchronize(current_stream()));
+  }
+  B200_CUDA_CHECK(cudaSetDevice(dev0));
 }

@@ -101,5 +101,13 @@ void convert(const void *in, void *out, i64 n, int direction) {
 
 }  // namespace
 
+void b200_int16_to_float_on(const short *d_in, i64 n, float *d_out, cudaStream_t stream) {
+  if (n <= 0) return;
+  const bool vec = ((((unsigned long long)d_in) | ((unsigned long long)d_out)) & 15ull) == 0;
+  i16_to_f32_kernel<<<grid_for(n), kThreads, 0, stream>>>(d_in, d_out, n, vec);
+  B200_CUDA_CHECK(cudaGetLastError());
+  b200_count_launch(1);
+}
+
 extern "C" void b200_int16_to_float(const short *data, long long n, float *res) { convert(data, res, n, 0); }
 extern "C" void b200_float_to_int16(const float *data, long long n, short *res) { convert(data, res, n, 1); }

@@ -8,6 +8,7 @@
 #define LIBSIMD_IMPLEMENTATION
 #include <simd/convolve.h>
 #include <simd/b200.h>
+#include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -25,10 +26,12 @@
     }                                                                                   \
   } while (0)
 
-static void run_full(B200Plan *plan, int algorithm, const float *x, size_t x_length,
-                     size_t x_stride, const float *h, size_t h_length, float *result,
-                     size_t result_stride, size_t batch, int reverse) {
+static void run_full_typed(B200Plan *plan, int algorithm, const float *x, size_t x_length,
+                           size_t x_stride, const float *h, size_t h_length, float *result,
+                           size_t result_stride, size_t batch, int reverse, int x_int16) {
   B200Job job;
+  memset(&job, 0, sizeof(job));
+  job.x_int16 = x_int16;
   job.x = x; job.x_len = (long long)x_length; job.x_stride = (long long)x_stride;
   job.h = h; job.h_len = (long long)h_length;
   job.out = result;
@@ -37,7 +40,15 @@ static void run_full(B200Plan *plan, int algorithm, const float *x, size_t x_len
   job.pad = (long long)h_length - 1;
   job.batch = (long long)batch;
   job.reverse = reverse;
-  b200_run(plan, algorithm, &job);
+  if (batch > 1) b200_run_multi(plan, algorithm, &job);   /* one GPU unless simd_b200_use_devices() said more */
+  else b200_run(plan, algorithm, &job);
+}
+
+static void run_full(B200Plan *plan, int algorithm, const float *x, size_t x_length,
+                     size_t x_stride, const float *h, size_t h_length, float *result,
+                     size_t result_stride, size_t batch, int reverse) {
+  run_full_typed(plan, algorithm, x, x_length, x_stride, h, h_length, result, result_stride,
+                 batch, reverse, 0);
 }
 
 /* reference: src/convolve.c:40-101 */
@@ -193,19 +204,19 @@ void convolve(ConvolutionHandle handle, const float *__restrict x,
 
 static void batch_dispatch(ConvolutionHandle handle, const float *x, size_t x_stride,
                            const float *h, float *result, size_t result_stride,
-                           size_t batch, int brute_reverse) {
+                           size_t batch, int brute_reverse, int x_int16) {
   SIMD_REQUIRE(x != NULL); SIMD_REQUIRE(h != NULL); SIMD_REQUIRE(result != NULL);
   size_t xl = (size_t)handle.x_length, hl = (size_t)handle.h_length;
   SIMD_REQUIRE(x_stride >= xl);
   SIMD_REQUIRE(result_stride >= xl + hl - 1);
   switch (handle.algorithm) {
     case kConvolutionAlgorithmFFT:
-      run_full((B200Plan *)handle.handle.fft.fft_plan, B200_ALG_FFT, x, xl, x_stride, h, hl,
-               result, result_stride, batch, handle.handle.fft.reverse);
+      run_full_typed((B200Plan *)handle.handle.fft.fft_plan, B200_ALG_FFT, x, xl, x_stride, h, hl,
+                     result, result_stride, batch, handle.handle.fft.reverse, x_int16);
       break;
     case kConvolutionAlgorithmOverlapSave:
-      run_full((B200Plan *)handle.handle.os.fft_plan, B200_ALG_OS, x, xl, x_stride, h, hl,
-               result, result_stride, batch, handle.handle.os.reverse);
+      run_full_typed((B200Plan *)handle.handle.os.fft_plan, B200_ALG_OS, x, xl, x_stride, h, hl,
+                     result, result_stride, batch, handle.handle.os.reverse, x_int16);
       break;
     case kConvolutionAlgorithmBruteForce:
       /* The handle was chosen for one signal.  A large batch can cross over to the fused
@@ -214,11 +225,11 @@ static void batch_dispatch(ConvolutionHandle handle, const float *x, size_t x_st
       /* profiling knob: VELES_B200_NO_BATCH_CROSSOVER=1 keeps the batch on the direct kernel */
       if (getenv("VELES_B200_NO_BATCH_CROSSOVER") ||
           simd_b200_select_algorithm_batch(xl, hl, batch) == kConvolutionAlgorithmBruteForce) {
-        run_full(NULL, B200_ALG_DIRECT, x, xl, x_stride, h, hl, result, result_stride, batch,
-                 brute_reverse);
+        run_full_typed(NULL, B200_ALG_DIRECT, x, xl, x_stride, h, hl, result, result_stride, batch,
+                       brute_reverse, x_int16);
       } else {
-        run_full(NULL, B200_ALG_OS, x, xl, x_stride, h, hl, result, result_stride, batch,
-                 brute_reverse);
+        run_full_typed(NULL, B200_ALG_OS, x, xl, x_stride, h, hl, result, result_stride, batch,
+                       brute_reverse, x_int16);
       }
       break;
   }
@@ -226,13 +237,24 @@ static void batch_dispatch(ConvolutionHandle handle, const float *x, size_t x_st
 
 void convolve_batch(ConvolutionHandle handle, const float *x, size_t x_stride,
                     const float *h, float *result, size_t result_stride, size_t batch) {
-  batch_dispatch(handle, x, x_stride, h, result, result_stride, batch, 0);
+  batch_dispatch(handle, x, x_stride, h, result, result_stride, batch, 0, 0);
+}
+
+void convolve_batch_int16(ConvolutionHandle handle, const int16_t *x, size_t x_stride,
+                          const float *h, float *result, size_t result_stride, size_t batch) {
+  batch_dispatch(handle, (const float *)(const void *)x, x_stride, h, result, result_stride, batch, 0, 1);
+}
+
+void cross_correlate_batch_int16(ConvolutionHandle handle, const int16_t *x, size_t x_stride,
+                                 const float *h, float *result, size_t result_stride,
+                                 size_t batch) {
+  batch_dispatch(handle, (const float *)(const void *)x, x_stride, h, result, result_stride, batch, 1, 1);
 }
 
 void cross_correlate_batch(ConvolutionHandle handle, const float *x, size_t x_stride,
                            const float *h, float *result, size_t result_stride,
                            size_t batch) {
-  batch_dispatch(handle, x, x_stride, h, result, result_stride, batch, 1);
+  batch_dispatch(handle, x, x_stride, h, result, result_stride, batch, 1, 0);
 }
 
 void simd_b200_filter_shard(const float *x, size_t x_length, const float *h,
@@ -247,6 +269,7 @@ void simd_b200_filter_shard(const float *x, size_t x_length, const float *h,
                     : B200_ALG_OS;
   }
   B200Job job;
+  memset(&job, 0, sizeof(job));
   job.x = x; job.x_len = (long long)x_length; job.x_stride = (long long)x_length;
   job.h = h; job.h_len = (long long)h_length;
   job.out = result; job.out_len = (long long)result_length;
@@ -258,6 +281,40 @@ void simd_b200_filter_shard(const float *x, size_t x_length, const float *h,
   b200_run(NULL, algorithm == B200_ALG_DIRECT ? B200_ALG_DIRECT : B200_ALG_OS, &job);
 }
 
+static int shard_algorithm(size_t result_length, size_t h_length) {
+  return simd_b200_select_algorithm(result_length, h_length) == kConvolutionAlgorithmBruteForce
+             ? B200_ALG_DIRECT
+             : B200_ALG_OS;
+}
+
+void simd_b200_filter_long(const float *x, size_t x_length, const float *h, size_t h_length,
+                           int reverse, float *result) {
+  SIMD_REQUIRE(x != NULL); SIMD_REQUIRE(h != NULL); SIMD_REQUIRE(result != NULL);
+  SIMD_REQUIRE(x_length > 0); SIMD_REQUIRE(h_length > 0);
+  B200Job job;
+  memset(&job, 0, sizeof(job));
+  job.x = x; job.x_len = (long long)x_length; job.x_stride = (long long)x_length;
+  job.h = h; job.h_len = (long long)h_length;
+  job.out = result; job.out_len = (long long)(x_length + h_length - 1);
+  job.out_stride = job.out_len;
+  job.pad = (long long)h_length - 1;
+  job.batch = 1;
+  job.reverse = reverse;
+  b200_run_multi(NULL, shard_algorithm(x_length + h_length - 1, h_length), &job);
+}
+
+void simd_b200_filter_long_sharded(int n_shards, const int *devices, float *const *x_shards,
+                                   const size_t *shard_lengths, const float *const *h_on_device,
+                                   size_t h_length, int reverse, float *const *result_shards) {
+  SIMD_REQUIRE(n_shards >= 1); SIMD_REQUIRE(h_length > 0);
+  size_t longest = 0;
+  for (int i = 0; i < n_shards; i++) if (shard_lengths[i] > longest) longest = shard_lengths[i];
+  b200_filter_long_sharded(n_shards, devices, x_shards, shard_lengths, h_on_device, h_length,
+                           reverse, result_shards, shard_algorithm(longest, h_length));
+}
+
+void simd_b200_use_devices(int n) { b200_use_devices(n); }
+int simd_b200_devices_in_use(void) { return b200_devices_in_use(); }
 void simd_b200_set_stream(void *cuda_stream) { b200_set_stream(cuda_stream); }
 void *simd_b200_get_stream(void) { return b200_get_stream(); }
 void simd_b200_synchronize(void) { b200_synchronize(); }

@@ -95,3 +95,27 @@ void cross_correlate(CrossCorrelationHandle handle, const float *__restrict x,
 }
 
 void cross_correlate_finalize(CrossCorrelationHandle handle) { convolve_finalize(handle); }
+
+/* ---- additive: correlate and keep only the extrema (simd/b200.h) ------------------------ */
+
+void b200_detect_peaks(const float *data, long long size, int type, void **results_host,
+                       size_t *count);
+
+void simd_b200_cross_correlate_peaks(CrossCorrelationHandle handle, const float *x,
+                                     const float *h, ExtremumType type,
+                                     ExtremumPoint **results, size_t *resultsLength) {
+  if (!x || !h || !results || !resultsLength) {
+    fprintf(stderr, "libSimd(b200): simd_b200_cross_correlate_peaks: null argument\n");
+    abort();
+  }
+  const size_t n = (size_t)handle.x_length + (size_t)handle.h_length - 1;
+  /* the correlation result never leaves the GPU: x and h go up, {position, value} pairs
+   * come down (reference chain: src/correlate.c:144-156 then src/detect_peaks.c:58-127) */
+  float *d_result = b200_device_alloc(n);
+  cross_correlate(handle, x, h, d_result);
+  void *host = NULL;
+  *resultsLength = 0;
+  if (n > 2) b200_detect_peaks(d_result, (long long)n, (int)type, &host, resultsLength);
+  *results = (ExtremumPoint *)host;
+  b200_device_free(d_result);
+}
