@@ -16,10 +16,12 @@ batched C-ABI entry point (convolve_batch) of libSimd.so.
   cpu_baseline  the reference's own convolve.c (oracle/_ref, + FFT stand-in) or the oracle
              port, all host cores, on a bounded sample of the same workload
 
-Workloads (BASELINE.json configs): c4 is the default headline (batched FFT/overlap-save
-regime, the largest batched configuration); c1/c2/c3/c5 are selectable for profiling.
-Under torchrun (N > 1) every rank processes the full per-GPU workload on its own GPU
-(independent signals, no data-path collective): weak scaling.
+Workloads (BASELINE.json configs): c4 is the headline (batched FFT/overlap-save regime, the
+largest batched configuration); with no --workload the line also carries a `configs` object
+with c1, c2, c3 and c5.  Under torchrun (N > 1) the batched configs are split by rows over
+the ranks (BASELINE: "sharded by batch"; total work fixed: strong scaling, no data-path
+collective), c5 is sharded contiguously with its (h-1)-sample halo exchanged point to point,
+c1/c2 run as replicas.
 """
 import argparse
 import json
@@ -195,72 +197,66 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--out-row-align", type=int, default=1,
-                    help="pad result rows to a multiple of this many floats (experiment)")
-    ap.add_argument("--no-profile", action="store_true",
-                    help="do not bracket kernels with events (they sit between the two launches of a step)")
-    ap.add_argument("--min-warm-s", type=float, default=0.6,
-                    help="keep stepping this long before the timed region so clock samples exist")
-    ap.add_argument("--algorithm", type=int, default=-1,
-                    help="force 0 direct / 2 overlap-save (profiling only)")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3)
-    if args.impl == "reference":
-        return run_reference_arm(args)
+def load_counters():
+    """ncu counters of the dominant kernel of each config (DRAM bytes, warp instructions per
+    launch), written by tools/ncu_counters.py from this round's captures, with the commit they
+    were taken at."""
+    for name in ("kernel_counters_r02.json", "traffic_r01.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            return json.load(open(p)), name
+    return {}, None
 
-    import torch
-    import torch.distributed as dist
-    import veles.simd_b200 as v
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    v.use_torch_stream()
+def load_fp32_peak():
+    p = os.path.join(ROOT, "profiles", "ffma_peak_r01.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["ffma_tflops"], "measured FFMA microbenchmark (tools/ffma_peak.cu -> profiles/ffma_peak_r01.json)"
+    return 74.45, "nominal 148 SM x 128 lanes x 2 x 1.965 GHz"
 
-    op, batch, x_len, h_len, desc = WORKLOADS[args.workload]
+
+class Ctx:
+    pass
+
+
+def bench_config(c, name, steps, warmup, min_warm_s=0.0, e2e_steps=3, do_e2e=True, do_pageable=False,
+                 algorithm=-1, no_profile=False, out_row_align=1):
+    """One BASELINE config on this rank's share of it.  Batched configs are split by rows over
+    the ranks (strong scaling: the batch is fixed); single-signal configs run as replicas."""
+    torch, dist, v = c.torch, c.dist, c.v
+    op, batch, x_len, h_len, desc = WORKLOADS[name]
     corr = op == "correlate"
     out_len = x_len + h_len - 1
-    if args.workload == "c5" and world > 1:
-        return run_sharded_long_signal(args, v, world, rank, local)
-    if args.workload == "peaks":
-        return run_detect_peaks(args, v, world, rank)
-    if args.workload == "minmax":
-        return run_minmax(args, v, world, rank)
-    if args.workload == "wavelet":
-        return run_wavelet(args, v, world, rank)
-    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
-    x = torch.rand((batch, x_len), generator=g, device="cuda") * 2 - 1
-    h = torch.rand((h_len,), generator=g, device="cuda") * 2 - 1
-    if args.out_row_align > 1:
-        pitch = -(-out_len // args.out_row_align) * args.out_row_align
-        y = torch.empty((batch, pitch), device="cuda")[:, :out_len]
+    from veles.simd_b200 import sharded
+    if batch > 1:
+        lo, hi = sharded.batch_rows(batch, c.rank, c.world)
+        sharding = f"rows [{lo},{hi}) of {batch} on this rank, no collective" if c.world > 1 else "one GPU"
     else:
-        y = torch.empty((batch, out_len), device="cuda")
+        lo, hi = 0, 1
+        sharding = "replicas only (a single small signal does not shard)" if c.world > 1 else "one GPU"
+    nb = hi - lo
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + c.rank)
+    x = torch.rand((nb, x_len), generator=g, device="cuda") * 2 - 1
+    gh = torch.Generator(device="cuda").manual_seed(0xC0FFEE)
+    h = torch.rand((h_len,), generator=gh, device="cuda") * 2 - 1
+    if out_row_align > 1:
+        pitch = -(-out_len // out_row_align) * out_row_align
+        y = torch.empty((nb, pitch), device="cuda")[:, :out_len]
+    else:
+        y = torch.empty((nb, out_len), device="cuda")
+    if batch == 1:
+        x, y = x[0], y[0]
     flush = None
-    in_bytes = x.numel() * 4
-    if in_bytes < 256 << 20:            # inputs smaller than L2 (126 MB): flush between steps
-        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    if x.numel() * 4 < 256 << 20:       # inputs smaller than L2 (126 MB): flush between steps
+        flush = c.flush
 
     handle = v.Handle(x_len, h_len, "", corr)
-    if args.algorithm == 0:
+    if algorithm == 0:
         os.environ["VELES_B200_NO_BATCH_CROSSOVER"] = "1"
-    if args.algorithm >= 0 and args.algorithm != handle.algorithm:
+    if algorithm >= 0 and algorithm != handle.algorithm:
         handle.close()
-        handle = ForcedHandle(v, x_len, h_len, corr, args.algorithm)
+        handle = ForcedHandle(v, x_len, h_len, corr, algorithm)
     alg = handle.algorithm
     n_fft = handle.transform_length if alg != 0 else 0
     if alg == 1:
@@ -271,191 +267,391 @@ def main():
             flush.zero_()
         handle(x, h, out=y)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # clocks are sampled from before the warm-up to the end of the timed region (the timed
-    # region alone can be shorter than one nvidia-smi sampling period)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     t_warm = time.perf_counter()
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     torch.cuda.synchronize()
-    while time.perf_counter() - t_warm < args.min_warm_s:      # keep the GPU busy until samples exist
+    while time.perf_counter() - t_warm < min_warm_s:      # keep the GPU busy until clock samples exist
         step()
         torch.cuda.synchronize()
-    barrier()
+    c.barrier()
     launches0 = v.lib.simd_b200_kernel_launches()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-          for _ in range(args.steps)]
-    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    c.barrier()
     for e0, e1 in ev:
         if flush is not None:
             flush.zero_()
         e0.record()
         handle(x, h, out=y)
         e1.record()
-    barrier()
+    c.barrier()
     launches = v.lib.simd_b200_kernel_launches() - launches0
     # Per-kernel durations for the roofline: the same steps once more with every launch
     # bracketed by its own event pair on the same stream.  Kept out of the loop above because
     # an event record between the two launches of a step defeats their programmatic
     # dependent launch (the fused kernel starts while the spectrum kernel still runs).
     prof = {"direct": (0.0, 0), "fused": (0.0, 0), "spectrum": (0.0, 0)}
-    if not args.no_profile:
+    if not no_profile:
         v.profile(True)
         v.profile_collect()
-        for _ in range(args.steps):
+        for _ in range(steps):
             if flush is not None:
                 flush.zero_()
             handle(x, h, out=y)
         torch.cuda.synchronize()
         prof = v.profile_collect()
         v.profile(False)
-    clocks = sampler.stop() if rank == 0 else None
     step_ms = [a.elapsed_time(b) for a, b in ev]
-    total_ms = sum(step_ms)
-    t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = t.item()
-    ms_per_step = total_ms / args.steps
-    outputs_per_step = batch * out_len * world
+    ms_per_step = c.max_over_ranks(sum(step_ms)) / steps
+    replicas = c.world if batch == 1 else 1
+    outputs_per_step = batch * out_len * replicas
     value = outputs_per_step / (ms_per_step * 1e-3) / 1e9
 
     # ---- roofline of the dominant kernel (per launch, from its own events) ----------------
     # the batched call may cross over from the handle's single-signal choice (selector.c)
-    if args.no_profile:      # no per-kernel events: charge the whole step to the dominant kernel
-        kname = "direct" if v.select_algorithm(x_len, h_len, batch) == 0 else "fused"
-        prof[kname] = (sum(step_ms), args.steps)
+    if no_profile:      # no per-kernel events: charge the whole step to the dominant kernel
+        kname = "direct" if v.select_algorithm(x_len, h_len, nb) == 0 else "fused"
+        prof[kname] = (sum(step_ms), steps)
     kind = "fused" if prof["fused"][1] > 0 else "direct"
     if kind == "fused" and alg == 0:
         alg = 2
         n_fft = v.transform_length(x_len, h_len)
     k_ms, k_cnt = prof[kind]
     k_avg_ms = k_ms / max(k_cnt, 1)
-    launches_per_step = max(k_cnt // args.steps, 1)
-    peaks, peak_src = load_peaks()
-    abytes = algorithmic_bytes(batch, x_len, h_len) / launches_per_step
-    aflops = algorithmic_flops(alg, batch, x_len, h_len, n_fft) / launches_per_step
+    launches_per_step = max(k_cnt // steps, 1)
+    abytes = algorithmic_bytes(nb, x_len, h_len) / launches_per_step
+    aflops = algorithmic_flops(alg, nb, x_len, h_len, n_fft) / launches_per_step
     ach_gbs = abytes / (k_avg_ms * 1e-3) / 1e9
     ach_tf = aflops / (k_avg_ms * 1e-3) / 1e12
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic_r01.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(args.workload, {}).get("dram_bytes_per_launch")
-    roofline = {"bound": "hbm", "achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": ach_gbs / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
-                "kernel": {"direct": "direct_kernel", "fused": "os_fused_kernel"}[kind],
+    cnt = c.counters.get(name, {}) if c.world == 1 else {}
+    traffic = cnt.get("dram_bytes_per_launch")
+    fp32_peak, fp32_src = c.fp32_peak
+    roofline = {"bound": "hbm", "achieved": ach_gbs, "peak": c.peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": ach_gbs / c.peaks["hbm_gbs"], "traffic": traffic, "peak_source": c.peak_src,
+                "kernel": cnt.get("kernel", {"direct": "direct_kernel", "fused": "os_fused_kernel"}[kind]),
                 "kernel_ms_per_launch": k_avg_ms, "kernel_launches_per_step": launches_per_step,
-                "kernel_share_of_step": min(1.0, k_avg_ms * launches_per_step / (sum(step_ms) / args.steps)),
+                "kernel_share_of_step": min(1.0, k_avg_ms * launches_per_step / (sum(step_ms) / steps)),
                 "timing": "per-launch event pairs on the launching stream, separate pass of the same steps",
                 "algorithmic_bytes_per_launch": abytes,
-                "fp32": {"achieved": ach_tf, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
-                         "frac": ach_tf / FP32_PEAK_TFLOPS,
-                         "peak_source": "measured FFMA microbenchmark (tools/ffma_peak.cu)",
+                "counters_from": ({"file": "profiles/" + c.counters_file, "commit": cnt.get("commit")}
+                                  if traffic else None),
+                "fp32": {"achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": ach_tf / fp32_peak, "peak_source": fp32_src,
                          "algorithmic_flops_per_launch": aflops}}
+    if cnt.get("warp_instructions_per_launch"):
+        # instruction-issue roofline: the kernel's own warp instructions at one per clock per
+        # scheduler (4 per SM); the FP pipe sustains 3.88 of those 4 (tools/fp_pipes.cu)
+        sm_clk = 148 * 4 * (c.peaks.get("sm_max_mhz", 1965.0) * 1e6)
+        floor_ms = cnt["warp_instructions_per_launch"] / sm_clk * 1e3
+        roofline["issue_frac"] = floor_ms / k_avg_ms
+        roofline["issue"] = {"warp_instructions_per_launch": cnt["warp_instructions_per_launch"],
+                             "floor_ms": floor_ms, "note": "time at one warp instruction per clock per scheduler / measured kernel time"}
+    if batch == 1 and x_len < 1 << 20:
+        roofline["note"] = "single small signal: launch/latency-bound, the fraction is not meaningful; see us_per_call"
 
-    # ---- end to end: same C-ABI call, host (pinned) buffers --------------------------------
+    # ---- end to end: same C-ABI call, HOST buffers ------------------------------------------
     e2e = None
-    if not args.no_e2e:
-        eb = batch
-        xh = torch.empty((eb, x_len), dtype=torch.float32).pin_memory()
+    if do_e2e:
+        shape_x = (nb, x_len) if batch > 1 else (x_len,)
+        shape_y = (nb, out_len) if batch > 1 else (out_len,)
+        xh = torch.empty(shape_x, dtype=torch.float32).pin_memory()
         hh = torch.empty((h_len,), dtype=torch.float32).pin_memory()
-        yh = torch.empty((eb, out_len), dtype=torch.float32).pin_memory()
-        xh.copy_(x[:eb].cpu() if eb * x_len < 2 ** 28 else torch.rand((eb, x_len)) * 2 - 1)
+        yh = torch.empty(shape_y, dtype=torch.float32).pin_memory()
+        if x.numel() < 2 ** 28:
+            xh.copy_(x.cpu())
+        else:
+            xh.uniform_(-1, 1)
         hh.copy_(h.cpu())
+        reps = e2e_steps if x.numel() >= 1 << 22 else 200          # tiny calls: time many
         handle(xh, hh, out=yh)            # warm-up (also sizes the staging buffers)
-        barrier()
+        c.barrier()
         t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
+        for _ in range(reps):
             handle(xh, hh, out=yh)        # returns with the result in host memory
-        torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dt = tt.item()
-        e2e = {"value": eb * out_len * world * args.e2e_steps / dt / 1e9, "unit": "GSamples/s",
-               "h2d_bytes_per_step": 4 * (eb * x_len + h_len), "d2h_bytes_per_step": 4 * eb * out_len,
-               "steps": args.e2e_steps, "ms_per_step": 1e3 * dt / args.e2e_steps,
-               "result_checksum": float(yh[0, :1024].double().sum())}
+        dt = c.max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": outputs_per_step * reps / dt / 1e9, "unit": "GSamples/s",
+               "h2d_bytes_per_step": 4 * (nb * x_len + h_len) * (c.world if batch > 1 else replicas),
+               "d2h_bytes_per_step": 4 * nb * out_len * (c.world if batch > 1 else replicas),
+               "steps": reps, "ms_per_step": 1e3 * dt / reps, "host_memory": "pinned",
+               "result_checksum": float(yh.reshape(-1)[:1024].double().sum())}
+        if batch == 1 and x_len < 1 << 20:
+            e2e["us_per_call"] = 1e6 * dt / reps
+        if do_pageable:
+            # what a caller of the reference API hands over: plain malloc'ed memory
+            import numpy as np
+            xp = np.empty(shape_x, np.float32)
+            xp[...] = xh.numpy()
+            yp = np.empty(shape_y, np.float32)
+            hp = hh.numpy().copy()
+            handle(xp, hp, out=yp)
+            c.barrier()
+            t0 = time.perf_counter()
+            for _ in range(max(reps // 2, 2) if reps < 50 else reps):
+                handle(xp, hp, out=yp)
+            n_p = max(reps // 2, 2) if reps < 50 else reps
+            dtp = c.max_over_ranks(time.perf_counter() - t0)
+            assert float(abs(yp.reshape(-1)[:1024].astype("float64").sum() - e2e["result_checksum"])) < 1e-3
+            e2e["pageable"] = {"value": outputs_per_step * n_p / dtp / 1e9, "unit": "GSamples/s",
+                               "ms_per_step": 1e3 * dtp / n_p, "steps": n_p,
+                               "host_memory": "pageable (numpy / malloc), what a reference caller passes"}
+            del xp, yp
         del xh, yh
     handle.close()
+    res = {"value": value, "unit": "GSamples/s", "ms_per_step": ms_per_step,
+           "workload": f"{name}: {desc}", "op": op, "signals_total": batch, "signals_this_rank": nb,
+           "x_length": x_len, "h_length": h_len,
+           "algorithm": {0: "direct", 1: "fft", 2: "overlap_save"}[alg], "transform_length": n_fft,
+           "scaling": "strong" if batch > 1 else "replicas", "sharding": sharding,
+           "l2": ("inputs larger than L2" if flush is None else "256 MiB flush buffer written between steps"),
+           "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
+           "step_ms": {"min": min(step_ms), "max": max(step_ms)}}
+    if batch == 1 and x_len < 1 << 20:
+        res["us_per_call"] = ms_per_step * 1e3
+    del x, y
+    torch.cuda.empty_cache()
+    return res
+
+
+def bench_c5_sharded(c, steps, warmup):
+    """C5 on N GPUs: the 2^30-sample signal is pre-sharded (contiguous, device resident);
+    each step = the (h-1)-sample halo exchange (NCCL send/recv) + the shard kernels.
+    Total work is fixed: strong scaling."""
+    torch, dist, v = c.torch, c.dist, c.v
+    from veles.simd_b200 import sharded
+    op, batch, x_len, h_len, desc = WORKLOADS["c5"]
+    s0, e0 = sharded.signal_range(x_len, c.rank, c.world)
+    ext, x_local = sharded.alloc_shard(e0 - s0, h_len - 1, device="cuda")
+    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + c.rank)
+    x_local.copy_(torch.rand((e0 - s0,), generator=g, device="cuda") * 2 - 1)
+    gh = torch.Generator(device="cuda").manual_seed(0xC0FFEE)
+    h = torch.rand((h_len,), generator=gh, device="cuda") * 2 - 1
+    n_out = (e0 - s0) + (h_len - 1 if c.rank == c.world - 1 else 0)
+    y = torch.empty((n_out,), device="cuda")
+
+    def step():
+        sharded.filter_long_signal(x_local, h, x_len, c.rank, c.world, sharded.gpu_compute, ext=ext, out=y,
+                                   overlap=bool(os.environ.get("VELES_B200_OVERLAP_HALO")))
+
+    for _ in range(warmup):
+        step()
+    c.barrier()
+    launches0 = v.lib.simd_b200_kernel_launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        step()
+    ev1.record()
+    c.barrier()
+    ms = c.max_over_ranks(ev0.elapsed_time(ev1)) / steps
+    # the exchange alone (same loop without the kernels), to say what it costs per step
+    xe0, xe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c.barrier()
+    xe0.record()
+    for _ in range(steps):
+        sharded.exchange_halo(x_local, h_len - 1, c.rank, c.world, into=ext[:h_len - 1] if c.rank > 0 else None)
+    xe1.record()
+    c.barrier()
+    ex_ms = c.max_over_ranks(xe0.elapsed_time(xe1)) / steps
+    res = {"value": (x_len + h_len - 1) / (ms * 1e-3) / 1e9, "unit": "GSamples/s", "ms_per_step": ms,
+           "workload": f"c5: {desc}", "scaling": "strong",
+           "sharding": "contiguous shards + (h-1)-sample halo via NCCL send/recv, pre-sharded device-resident data",
+           "halo_bytes_per_rank": 4 * (h_len - 1), "halo_exchange_ms": ex_ms,
+           "l2": "inputs larger than L2",
+           "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0), "e2e": None, "roofline": None}
+    del x_local, ext, y
+    torch.cuda.empty_cache()
+    return res
+
+
+def e2e_single_process(c, name, steps):
+    """Rank 0 alone: the whole batch in host memory through one convolve_batch call that spreads
+    it over all the GPUs of the box (simd_b200_use_devices), other ranks idle."""
+    torch, v = c.torch, c.v
+    op, batch, x_len, h_len, desc = WORKLOADS[name]
+    out_len = x_len + h_len - 1
+    xh = torch.empty((batch, x_len), dtype=torch.float32).pin_memory()
+    xh.uniform_(-1, 1)
+    hh = torch.rand((h_len,), dtype=torch.float32).pin_memory()
+    yh = torch.empty((batch, out_len), dtype=torch.float32).pin_memory()
+    n = v.use_devices(c.world)
+    with v.Handle(x_len, h_len, "", op == "correlate") as hd:
+        hd(xh, hh, out=yh)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            hd(xh, hh, out=yh)
+        dt = time.perf_counter() - t0
+    v.use_devices(1)
+    return {"value": batch * out_len * steps / dt / 1e9, "unit": "GSamples/s", "ms_per_step": 1e3 * dt / steps,
+            "devices": n, "steps": steps, "h2d_bytes_per_step": 4 * (batch * x_len + h_len),
+            "d2h_bytes_per_step": 4 * batch * out_len, "host_memory": "pinned",
+            "how": "one process, one convolve_batch call, simd_b200_use_devices(N): one worker thread + pipeline per GPU"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="one workload only (default: c4 as the headline plus every other BASELINE config)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="headline only")
+    ap.add_argument("--out-row-align", type=int, default=1,
+                    help="pad result rows to a multiple of this many floats (experiment)")
+    ap.add_argument("--no-profile", action="store_true",
+                    help="do not bracket kernels with events (they sit between the two launches of a step)")
+    ap.add_argument("--min-warm-s", type=float, default=0.6,
+                    help="keep stepping this long before the timed region so clock samples exist")
+    ap.add_argument("--algorithm", type=int, default=-1,
+                    help="force 0 direct / 2 overlap-save (profiling only)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    all_configs = args.workload is None and not args.no_configs
+    if args.workload is None:
+        args.workload = "c4"
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    import veles.simd_b200 as v
+
+    c = Ctx()
+    c.torch, c.dist, c.v = torch, dist, v
+    c.world = int(os.environ.get("WORLD_SIZE", "1"))
+    c.rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    if c.world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    v.use_torch_stream()
+    c.peaks, c.peak_src = load_peaks()
+    c.counters, c.counters_file = load_counters()
+    c.fp32_peak = load_fp32_peak()
+    c.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        if c.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(val):
+        if c.world == 1:
+            return val
+        t = torch.tensor([val], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    c.barrier, c.max_over_ranks = barrier, max_over_ranks
+    world, rank = c.world, c.rank
+
+    if args.workload == "peaks":
+        return run_detect_peaks(args, v, world, rank)
+    if args.workload == "minmax":
+        return run_minmax(args, v, world, rank)
+    if args.workload == "wavelet":
+        return run_wavelet(args, v, world, rank)
+
+    # clocks are sampled from before the warm-up to the end of the timed region (the timed
+    # region alone can be shorter than one nvidia-smi sampling period)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    if args.workload == "c5" and world > 1:
+        head = bench_c5_sharded(c, args.steps, args.warmup)
+    else:
+        head = bench_config(c, args.workload, args.steps, args.warmup, min_warm_s=args.min_warm_s,
+                            e2e_steps=args.e2e_steps, do_e2e=not args.no_e2e, do_pageable=not args.no_e2e,
+                            algorithm=args.algorithm, no_profile=args.no_profile,
+                            out_row_align=args.out_row_align)
+    clocks = sampler.stop() if rank == 0 else None
+
+    configs = {}
+    if all_configs:
+        # every other BASELINE config, fewer steps each; at N > 1 the batched ones are split by
+        # rows (strong scaling), C5 is sharded with its halo, C1/C2 run as replicas
+        for name in ("c1", "c2", "c3", "c5"):
+            st = max(10, min(args.steps, 30)) if name != "c5" else max(5, min(args.steps, 10))
+            try:
+                if name == "c5" and world > 1:
+                    configs[name] = bench_c5_sharded(c, st, args.warmup)
+                else:
+                    configs[name] = bench_config(c, name, st, args.warmup, e2e_steps=2, do_e2e=not args.no_e2e)
+            except Exception as e:          # one config must not take the headline down
+                configs[name] = {"error": f"{type(e).__name__}: {e}"}
+    single = None
+    if world > 1 and not args.no_e2e and WORKLOADS[args.workload][1] > 1:
+        barrier()
+        if rank == 0:
+            try:
+                single = e2e_single_process(c, args.workload, args.e2e_steps)
+            except Exception as e:
+                single = {"error": f"{type(e).__name__}: {e}"}
+        barrier()
 
     base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         base, _, _ = cpu_baseline(args.workload)
+        base["fft_note"] = fft_standin_note()
+        if all_configs:
+            for name in configs:
+                if "error" not in configs[name]:
+                    b, _, _ = cpu_baseline(name, target_s=1.0)
+                    configs[name]["cpu_baseline"] = b
 
     if rank == 0:
-        line = {"metric": "conv1d_output_gsamples_per_s", "value": value, "unit": "GSamples/s",
+        line = {"metric": "conv1d_output_gsamples_per_s", "value": head["value"], "unit": "GSamples/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+                "scaling": head["scaling"] if head["scaling"] != "replicas" else "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"{args.workload}: {desc}", "op": op,
-                           "signals_per_gpu": batch, "x_length": x_len, "h_length": h_len,
-                           "algorithm": {0: "direct", 1: "fft", 2: "overlap_save"}[alg],
-                           "transform_length": n_fft,
-                           "l2": ("inputs larger than L2" if flush is None
-                                  else "256 MiB flush buffer written between steps"),
-                           "sharding": "independent signals per rank, no collective"},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
-                "roofline": roofline, "cpu_baseline": base,
-                "step_ms": {"min": min(step_ms), "max": max(step_ms)}}
+                "config": {k: head[k] for k in ("workload", "op", "signals_total", "signals_this_rank", "x_length",
+                                                "h_length", "algorithm", "transform_length", "l2", "sharding")
+                           if k in head},
+                "clocks": clocks, "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
+                "roofline": head.get("roofline"), "cpu_baseline": base}
+        for k in ("step_ms", "halo_bytes_per_rank", "halo_exchange_ms", "us_per_call"):
+            if k in head:
+                line[k] = head[k]
+        if single is not None:
+            line["e2e_single_process"] = single
+        if configs:
+            line["configs"] = configs
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_sharded_long_signal(args, v, world, rank, local):
-    """C5 on N GPUs: the 2^30-sample signal is pre-sharded (contiguous, device resident);
-    each step = the (h-1)-sample halo exchange (NCCL send/recv) + the shard kernels.
-    Total work is fixed, so this line reports strong scaling."""
-    import torch
-    import torch.distributed as dist
-    from veles.simd_b200 import sharded
-    op, batch, x_len, h_len, desc = WORKLOADS["c5"]
-    s0, e0 = sharded.signal_range(x_len, rank, world)
-    ext, x_local = sharded.alloc_shard(e0 - s0, h_len - 1, device="cuda")
-    g = torch.Generator(device="cuda").manual_seed(0xC0FFEE + rank)
-    x_local.copy_(torch.rand((e0 - s0,), generator=g, device="cuda") * 2 - 1)
-    gh = torch.Generator(device="cuda").manual_seed(0xC0FFEE)
-    h = torch.rand((h_len,), generator=gh, device="cuda") * 2 - 1
-    n_out = (e0 - s0) + (h_len - 1 if rank == world - 1 else 0)
-    y = torch.empty((n_out,), device="cuda")
-
-    def step():
-        sharded.filter_long_signal(x_local, h, x_len, rank, world, sharded.gpu_compute, ext=ext, out=y,
-                                   overlap=bool(os.environ.get("VELES_B200_OVERLAP_HALO")))
-
-    for _ in range(args.warmup):
-        step()
-    dist.barrier(); torch.cuda.synchronize()
-    launches0 = v.lib.simd_b200_kernel_launches()
-    e0_, e1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0_.record()
-    for _ in range(args.steps):
-        step()
-    e1_.record()
-    dist.barrier(); torch.cuda.synchronize()
-    t = torch.tensor([e0_.elapsed_time(e1_)], device="cuda", dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = t.item() / args.steps
-    if rank == 0:
-        line = {"metric": "conv1d_output_gsamples_per_s", "value": (x_len + h_len - 1) / (ms * 1e-3) / 1e9,
-                "unit": "GSamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"c5: {desc}", "sharding": "contiguous shards + (h-1) halo via NCCL send/recv",
-                           "l2": "inputs larger than L2"},
-                "gpu_launches": int(v.lib.simd_b200_kernel_launches() - launches0),
-                "e2e": None, "roofline": None, "cpu_baseline": None, "clocks": None}
-        print(json.dumps(line), flush=True)
-    dist.destroy_process_group()
+def fft_standin_note():
+    """How fast the CPU arm's FFT is, so that a reader can scale the ratio to a SIMD FFT:
+    single-core MFLOP/s (5 N log2 N convention) of the stand-in on a 16384-point real transform
+    pair, via the oracle's overlap-save call."""
+    try:
+        import numpy as np
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from _oracle import Reference, have_reference, Oracle
+        impl = Reference() if have_reference() else Oracle()
+        x = np.random.default_rng(0).uniform(-1, 1, 1 << 20).astype(np.float32)
+        h = np.random.default_rng(1).uniform(-1, 1, 4096).astype(np.float32)
+        run = (lambda: impl.convolve_batch(x[None, :], h, reverse=0, algorithm=-1, threads=1)) if have_reference() \
+            else (lambda: impl.convolve_batch(x[None, :], h, reverse=0, threads=1))
+        run()
+        t0 = time.perf_counter()
+        run()
+        dt = time.perf_counter() - t0
+        L, step = 16384, 16384 - 4095
+        nseg = -(-(x.size + h.size - 1) // step)
+        flops = nseg * 2 * 2.5 * L * 14
+        return {"single_core_mflops": flops / dt / 1e6,
+                "what": "FFTF is absent from the reference tree; the CPU arm transforms with oracle/fft_pow2.h, "
+                        "scalar radix-4 C at -O2. A SIMD FFT library typically sustains several GFLOP/s per "
+                        "core: scale the GPU/CPU ratios down by that factor over single_core_mflops."}
+    except Exception as e:      # the note must never break the bench line
+        return {"error": str(e)}
 
 
 def run_detect_peaks(args, v, world, rank):

@@ -8,6 +8,9 @@
 // entry point aborts with a message.
 #include "b200_device.cuh"
 #include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <functional>
 #include <mutex>
 #include <string.h>
 #include <thread>
@@ -28,7 +31,104 @@ struct Pipe {           // copy streams / events of the host-pointer pipeline
   bool ready = false;
   cudaStream_t s_in = nullptr, s_out = nullptr;
   cudaEvent_t ev_in[2], ev_comp[2], ev_out[2];
+  // pinned bounce slots for callers whose buffers are pageable (malloc / mallocf memory, what
+  // a caller of the reference API has): created on first use, grow-only
+  char *pin_in[2] = {nullptr, nullptr}, *pin_out[2] = {nullptr, nullptr};
+  size_t pin_in_cap[2] = {0, 0}, pin_out_cap[2] = {0, 0};
 };
+
+// A handful of host threads that copy between pageable and pinned memory.  cudaMemcpyAsync on
+// pageable memory is staged by the driver on the calling thread at ~11 GB/s (H2D) and does not
+// overlap with anything (tools/h2d_ceiling.cu); one memcpy thread manages ~14 GB/s, several
+// together keep a PCIe 5 x16 link (~50 GB/s per direction) busy.
+class CopyPool {
+ public:
+  static CopyPool &get() {
+    // never destroyed: its detached workers sleep on the condition variable until the process
+    // ends, and a static destructor would pull it from under them (exit() would hang)
+    static CopyPool *pool = new CopyPool;
+    return *pool;
+  }
+  int threads() const { return (int)workers_.size(); }
+  // copies `rows` rows of `width` bytes (pitches in bytes); returns when all of it is done
+  void copy2d(char *dst, size_t dst_pitch, const char *src, size_t src_pitch, size_t width, size_t rows) {
+    if (width == 0 || rows == 0) return;
+    const size_t chunk = (size_t)2 << 20;
+    std::vector<std::function<void()>> tasks;
+    if (dst_pitch == width && src_pitch == width) {       // one contiguous block
+      const size_t total = width * rows;
+      for (size_t off = 0; off < total; off += chunk) {
+        const size_t n = total - off < chunk ? total - off : chunk;
+        tasks.emplace_back([=]() { memcpy(dst + off, src + off, n); });
+      }
+    } else {
+      size_t rows_per = chunk / width > 0 ? chunk / width : 1;
+      for (size_t r0 = 0; r0 < rows; r0 += rows_per) {
+        const size_t r1 = r0 + rows_per < rows ? r0 + rows_per : rows;
+        tasks.emplace_back([=]() {
+          for (size_t r = r0; r < r1; r++) memcpy(dst + r * dst_pitch, src + r * src_pitch, width);
+        });
+      }
+    }
+    run(tasks);
+  }
+
+ private:
+  CopyPool() {
+    unsigned hc = std::thread::hardware_concurrency();
+    int n = (int)(hc / 2);
+    if (n < 2) n = 2;
+    if (n > 12) n = 12;
+    for (int i = 0; i < n; i++) workers_.emplace_back([this]() { loop(); });
+    for (auto &w : workers_) w.detach();                  // live for the life of the process
+  }
+  struct Batch { std::atomic<size_t> left; std::mutex m; std::condition_variable cv; };
+  void run(std::vector<std::function<void()>> &tasks) {
+    if (tasks.size() == 1) { tasks[0](); return; }
+    Batch b;
+    b.left.store(tasks.size());
+    {
+      std::lock_guard<std::mutex> lock(m_);
+      for (auto &t : tasks) q_.emplace_back(&b, std::move(t));
+    }
+    cv_.notify_all();
+    std::unique_lock<std::mutex> lock(b.m);
+    b.cv.wait(lock, [&]() { return b.left.load() == 0; });
+  }
+  void loop() {
+    for (;;) {
+      std::pair<Batch *, std::function<void()>> job;
+      {
+        std::unique_lock<std::mutex> lock(m_);
+        cv_.wait(lock, [&]() { return !q_.empty(); });
+        job = std::move(q_.front());
+        q_.pop_front();
+      }
+      job.second();
+      Batch *b = job.first;
+      std::lock_guard<std::mutex> lock(b->m);           // the waiter cannot leave before we are out
+      if (b->left.fetch_sub(1) == 1) b->cv.notify_all();
+    }
+  }
+  std::vector<std::thread> workers_;
+  std::mutex m_;
+  std::condition_variable cv_;
+  std::deque<std::pair<Batch *, std::function<void()>>> q_;
+};
+
+bool is_pageable_host(const void *p) {
+  cudaPointerAttributes attr;
+  cudaError_t err = cudaPointerGetAttributes(&attr, p);
+  if (err != cudaSuccess) { cudaGetLastError(); return true; }
+  return attr.type == cudaMemoryTypeUnregistered;
+}
+
+void grow_pinned(char **buf, size_t *cap, size_t need) {
+  if (need <= *cap) return;
+  if (*buf) B200_CUDA_CHECK(cudaFreeHost(*buf));
+  B200_CUDA_CHECK(cudaHostAlloc(buf, need, cudaHostAllocDefault));
+  *cap = need;
+}
 
 // Host-pointer calls too small for the pipeline below to pay (a reference-API caller hands
 // over a few KB per call): one pinned, device-mapped bounce buffer per device.
@@ -425,6 +525,22 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
   const i64 piece_o = slice_time ? outs_per_piece : rows_per_piece * o_row;
   const i64 n_pieces = slice_time ? (o_row + outs_per_piece - 1) / outs_per_piece
                                   : (job->batch + rows_per_piece - 1) / rows_per_piece;
+  // pageable caller memory goes through the pinned bounce slots (worth it from ~1 MiB per piece)
+  const size_t es = job->x_int16 ? sizeof(short) : sizeof(float);
+  const bool x_page = !xd && (size_t)piece_x * es >= ((size_t)1 << 20) && is_pageable_host(job->x);
+  const bool o_page = !od && (size_t)piece_o * 4 >= ((size_t)1 << 20) && is_pageable_host(job->out);
+  for (int sl = 0; sl < (n_pieces > 1 ? 2 : 1); sl++) {
+    if (x_page) grow_pinned(&pipe.pin_in[sl], &pipe.pin_in_cap[sl], (size_t)piece_x * es);
+    if (o_page) grow_pinned(&pipe.pin_out[sl], &pipe.pin_out_cap[sl], (size_t)piece_o * 4);
+  }
+  struct Unload { float *dst; i64 len, rows, pitch; int slot; bool pending; } prev = {nullptr, 0, 0, 0, 0, false};
+  auto unload = [&](Unload &u) {          // pinned bounce slot -> the caller's result rows
+    if (!u.pending) return;
+    B200_CUDA_CHECK(cudaEventSynchronize(pipe.ev_out[u.slot]));
+    CopyPool::get().copy2d(reinterpret_cast<char *>(u.dst), sizeof(float) * (size_t)u.pitch, pipe.pin_out[u.slot],
+                           sizeof(float) * (size_t)u.len, sizeof(float) * (size_t)u.len, (size_t)u.rows);
+    u.pending = false;
+  };
   for (int sl = 0; sl < (n_pieces > 1 ? 2 : 1); sl++) {
     if (!xd) grow(&st->x[sl], &st->x_cap[sl], (size_t)piece_x);
     if (job->x_int16) grow(&st->x16[sl], &st->x16_cap[sl], ((size_t)piece_x + 1) / 2);
@@ -460,29 +576,40 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     src_x = job->x_int16 ? nullptr : job->x + x_off;
     dj.batch = p_rows; dj.x_len = px_len; dj.out_len = po_len; dj.pad = p_pad;
     // --- H2D ------------------------------------------------------------------------------
+    // the caller's rows as the copy engine will read them: in place, or compacted into the
+    // pinned bounce slot by the copy threads
+    const char *h2d_src = reinterpret_cast<const char *>(job->x) + (size_t)x_off * es;
+    i64 h2d_pitch = job->x_stride;
+    if (x_page && px_len > 0) {
+      if (pi >= 2) B200_CUDA_CHECK(cudaEventSynchronize(pipe.ev_in[sl]));   // slot's last H2D has read it
+      CopyPool::get().copy2d(pipe.pin_in[sl], es * (size_t)px_len, h2d_src, es * (size_t)job->x_stride,
+                             es * (size_t)px_len, (size_t)p_rows);
+      h2d_src = pipe.pin_in[sl];
+      h2d_pitch = px_len;
+    }
     if (!xd) {
       if (pi >= 2) B200_CUDA_CHECK(cudaStreamWaitEvent(pipe.s_in, pipe.ev_comp[sl], 0));
       if (px_len > 0 && job->x_int16) {
         // 2 bytes per sample over PCIe; widened to float on the device, into the slot the
         // kernels read (reference converter: inc/simd/arithmetic.h:231-278)
-        const short *src16 = reinterpret_cast<const short *>(job->x) + x_off;
+        const short *src16 = reinterpret_cast<const short *>(h2d_src);
         short *dst16 = reinterpret_cast<short *>(st->x16[sl]);
-        if (p_rows == 1 || job->x_stride == px_len) {
+        if (p_rows == 1 || h2d_pitch == px_len) {
           B200_CUDA_CHECK(cudaMemcpyAsync(dst16, src16, sizeof(short) * px_len * p_rows,
                                           cudaMemcpyHostToDevice, pipe.s_in));
         } else {
           B200_CUDA_CHECK(cudaMemcpy2DAsync(dst16, sizeof(short) * px_len, src16,
-                                            sizeof(short) * job->x_stride, sizeof(short) * px_len,
+                                            sizeof(short) * h2d_pitch, sizeof(short) * px_len,
                                             (size_t)p_rows, cudaMemcpyHostToDevice, pipe.s_in));
         }
         b200_int16_to_float_on(dst16, px_len * p_rows, st->x[sl], pipe.s_in);
       } else if (px_len > 0) {
-        if (p_rows == 1 || job->x_stride == px_len) {   // contiguous: no 2-D pitch limit
-          B200_CUDA_CHECK(cudaMemcpyAsync(st->x[sl], src_x, sizeof(float) * px_len * p_rows,
+        if (p_rows == 1 || h2d_pitch == px_len) {   // contiguous: no 2-D pitch limit
+          B200_CUDA_CHECK(cudaMemcpyAsync(st->x[sl], h2d_src, sizeof(float) * px_len * p_rows,
                                           cudaMemcpyHostToDevice, pipe.s_in));
         } else {
-          B200_CUDA_CHECK(cudaMemcpy2DAsync(st->x[sl], sizeof(float) * px_len, src_x,
-                                            sizeof(float) * job->x_stride, sizeof(float) * px_len,
+          B200_CUDA_CHECK(cudaMemcpy2DAsync(st->x[sl], sizeof(float) * px_len, h2d_src,
+                                            sizeof(float) * h2d_pitch, sizeof(float) * px_len,
                                             (size_t)p_rows, cudaMemcpyHostToDevice, pipe.s_in));
         }
       }
@@ -506,7 +633,16 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
     }
     B200_CUDA_CHECK(cudaEventRecord(pipe.ev_comp[sl], stream));
     // --- D2H ------------------------------------------------------------------------------
-    if (!od) {
+    if (o_page) {
+      // into the pinned slot; the copy threads move the previous piece to the caller's rows
+      // while this one is on the GPU
+      B200_CUDA_CHECK(cudaStreamWaitEvent(pipe.s_out, pipe.ev_comp[sl], 0));
+      B200_CUDA_CHECK(cudaMemcpyAsync(pipe.pin_out[sl], st->out[sl], sizeof(float) * po_len * p_rows,
+                                      cudaMemcpyDeviceToHost, pipe.s_out));
+      B200_CUDA_CHECK(cudaEventRecord(pipe.ev_out[sl], pipe.s_out));
+      unload(prev);
+      prev = Unload{dst_o, po_len, p_rows, p_rows == 1 ? po_len : job->out_stride, sl, true};
+    } else if (!od) {
       B200_CUDA_CHECK(cudaStreamWaitEvent(pipe.s_out, pipe.ev_comp[sl], 0));
       if (p_rows == 1 || job->out_stride == po_len) {
         B200_CUDA_CHECK(cudaMemcpyAsync(dst_o, st->out[sl], sizeof(float) * po_len * p_rows,
@@ -519,6 +655,7 @@ extern "C" void b200_run(B200Plan *plan, int algorithm, const B200Job *job) {
       B200_CUDA_CHECK(cudaEventRecord(pipe.ev_out[sl], pipe.s_out));
     }
   }
+  unload(prev);
   if (!od) B200_CUDA_CHECK(cudaStreamSynchronize(pipe.s_out));
   B200_CUDA_CHECK(cudaStreamSynchronize(stream));
 }
