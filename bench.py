@@ -469,10 +469,14 @@ def e2e_single_process(c, name, steps):
     torch, v = c.torch, c.v
     op, batch, x_len, h_len, desc = WORKLOADS[name]
     out_len = x_len + h_len - 1
-    xh = torch.empty((batch, x_len), dtype=torch.float32).pin_memory()
-    xh.uniform_(-1, 1)
-    hh = torch.rand((h_len,), dtype=torch.float32).pin_memory()
-    yh = torch.empty((batch, out_len), dtype=torch.float32).pin_memory()
+    import numpy as np
+    # the library's own pinned allocator (portable: every GPU's copy engine reads it in place)
+    xa, ya = v.PinnedArray((batch, x_len)), v.PinnedArray((batch, out_len))
+    xh, yh = xa.array, ya.array
+    rng = np.random.default_rng(0xC0FFEE)
+    for b0 in range(0, batch, 64):
+        xh[b0:b0 + 64] = rng.uniform(-1, 1, xh[b0:b0 + 64].shape).astype(np.float32)
+    hh = rng.uniform(-1, 1, h_len).astype(np.float32)
     n = v.use_devices(c.world)
     with v.Handle(x_len, h_len, "", op == "correlate") as hd:
         hd(xh, hh, out=yh)
@@ -481,6 +485,7 @@ def e2e_single_process(c, name, steps):
             hd(xh, hh, out=yh)
         dt = time.perf_counter() - t0
     v.use_devices(1)
+    xa.close(); ya.close()
     return {"value": batch * out_len * steps / dt / 1e9, "unit": "GSamples/s", "ms_per_step": 1e3 * dt / steps,
             "devices": n, "steps": steps, "h2d_bytes_per_step": 4 * (batch * x_len + h_len),
             "d2h_bytes_per_step": 4 * batch * out_len, "host_memory": "pinned",

@@ -32,6 +32,15 @@ void cross_correlate_batch(struct ConvolutionHandle handle, const float *x, size
                            const float *h, float *result, size_t result_stride,
                            size_t batch) NOTNULL(2, 4, 5);
 
+/* ---- pinned host buffers ---------------------------------------------------------------
+ * mallocf() (simd/memory.h, reference src/memory.c:89-91) returns pageable memory, which the
+ * GPU's copy engines cannot read in place: the library then moves it through pinned bounce
+ * buffers with a few copy threads (about half the rate of pinned memory end to end).  A
+ * caller that can choose its allocator gets the full host-link rate with these two; the
+ * memory is page-locked and usable from every GPU.  Release with simd_b200_free_pinned(). */
+float *simd_b200_mallocf_pinned(size_t length);
+void simd_b200_free_pinned(float *ptr);
+
 /* ---- fewer bytes over PCIe for host-pointer callers -----------------------------------
  * A drop-in caller hands over host memory, and end to end such a call is bound by the host
  * link, not by the kernels (BENCH: ~45 GB/s each way against ~2.3 TB/s of kernel traffic).

@@ -103,6 +103,10 @@ def _load():
     L.simd_b200_cross_correlate_peaks.restype = None
     L.simd_b200_filter_shard.argtypes = [vp, sz, vp, sz, C.c_int, sz, vp, sz, C.c_int]
     L.simd_b200_filter_shard.restype = None
+    L.simd_b200_mallocf_pinned.argtypes = [sz]
+    L.simd_b200_mallocf_pinned.restype = vp
+    L.simd_b200_free_pinned.argtypes = [vp]
+    L.simd_b200_free_pinned.restype = None
     L.simd_b200_use_devices.argtypes = [C.c_int]
     L.simd_b200_use_devices.restype = None
     L.simd_b200_devices_in_use.restype = C.c_int
@@ -181,7 +185,7 @@ EXPORTED_SYMBOLS = (
     "cross_correlate_overlap_save_finalize cross_correlate_initialize cross_correlate "
     "cross_correlate_finalize mallocf malloc_aligned memsetf rmemcpyf convolve_batch "
     "cross_correlate_batch simd_b200_filter_shard simd_b200_select_algorithm "
-    "simd_b200_select_algorithm_batch simd_b200_use_devices simd_b200_devices_in_use "
+    "simd_b200_select_algorithm_batch simd_b200_mallocf_pinned simd_b200_free_pinned simd_b200_use_devices simd_b200_devices_in_use "
     "simd_b200_filter_long simd_b200_filter_long_sharded convolve_batch_int16 "
     "cross_correlate_batch_int16 simd_b200_cross_correlate_peaks "
     "simd_b200_transform_length simd_b200_set_stream simd_b200_get_stream "
@@ -480,6 +484,27 @@ def cross_correlate_peaks(x, h, type_=EXTREMUM_BOTH):
     raw = np.ctypeslib.as_array(C.cast(res, C.POINTER(C.c_int32)), shape=(n.value, 2)).copy()
     C.CDLL(None).free(res)
     return raw[:, 0].copy(), raw[:, 1].copy().view(np.float32)
+
+
+class PinnedArray:
+    """numpy view of simd_b200_mallocf_pinned memory (freed with the object)."""
+
+    def __init__(self, shape):
+        n = int(np.prod(shape))
+        self.ptr = lib.simd_b200_mallocf_pinned(n)
+        self.array = np.ctypeslib.as_array(C.cast(self.ptr, C.POINTER(C.c_float)), shape=(n,)).reshape(shape)
+
+    def close(self):
+        if self.ptr:
+            self.array = None
+            lib.simd_b200_free_pinned(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def use_devices(n):

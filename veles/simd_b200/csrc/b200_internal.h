@@ -45,6 +45,8 @@ typedef struct B200Plan B200Plan;   /* opaque; lives behind handle.fft_plan */
 B200Plan *b200_plan_create(int algorithm, long long x_len, long long h_len, int n_fft,
                            int real_packed);
 void b200_plan_destroy(B200Plan *plan);
+float *b200_host_alloc_pinned(size_t floats);      /* cudaHostAlloc(portable) / cudaFreeHost */
+void b200_host_free_pinned(float *p);
 float *b200_device_alloc(size_t floats);           /* cudaMalloc / cudaFree on the current device */
 void b200_device_free(float *p);
 float *b200_plan_spectrum(const B200Plan *plan);   /* device pointer */

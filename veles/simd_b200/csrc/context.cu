@@ -342,6 +342,18 @@ extern "C" void b200_plan_destroy(B200Plan *plan) {
   delete plan;
 }
 
+// pinned host memory for callers that do not link the CUDA runtime themselves (portable: every
+// GPU's copy engine reads it in place, which is what the multi-GPU host-pointer path wants)
+extern "C" float *b200_host_alloc_pinned(size_t floats) {
+  float *p = nullptr;
+  current_device();     // aborts with a message when there is no usable GPU
+  B200_CUDA_CHECK(cudaHostAlloc(&p, sizeof(float) * (floats ? floats : 1), cudaHostAllocPortable));
+  return p;
+}
+extern "C" void b200_host_free_pinned(float *p) {
+  if (p) B200_CUDA_CHECK(cudaFreeHost(p));
+}
+
 // plain device buffers for the host layer (cross-correlate -> peaks keeps its result here)
 extern "C" float *b200_device_alloc(size_t floats) {
   float *p = nullptr;

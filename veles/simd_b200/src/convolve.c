@@ -313,6 +313,8 @@ void simd_b200_filter_long_sharded(int n_shards, const int *devices, float *cons
                            reverse, result_shards, shard_algorithm(longest, h_length));
 }
 
+float *simd_b200_mallocf_pinned(size_t length) { return b200_host_alloc_pinned(length); }
+void simd_b200_free_pinned(float *ptr) { b200_host_free_pinned(ptr); }
 void simd_b200_use_devices(int n) { b200_use_devices(n); }
 int simd_b200_devices_in_use(void) { return b200_devices_in_use(); }
 void simd_b200_set_stream(void *cuda_stream) { b200_set_stream(cuda_stream); }
