@@ -463,6 +463,64 @@ def bench_c5_sharded(c, steps, warmup):
     return res
 
 
+def e2e_fewer_bytes(c, steps=2):
+    """The two PCIe-saving chains (simd/b200.h), end to end with pinned host buffers, next to the
+    plain calls they replace: (1) C4 with int16 samples widened on the device; (2) correlate a
+    2^26-sample signal with a 512-tap template and return only the extrema."""
+    import numpy as np
+    torch, v = c.torch, c.v
+    out = {}
+    # (1) int16 input, C4 shape
+    _, batch, x_len, h_len, _ = WORKLOADS["c4"]
+    out_len = x_len + h_len - 1
+    x16 = torch.empty((batch, x_len), dtype=torch.int16).pin_memory()
+    x16.random_(-32768, 32767)
+    hh = (torch.rand((h_len,)) * 2 - 1).pin_memory()
+    yh = torch.empty((batch, out_len), dtype=torch.float32).pin_memory()
+    with v.Handle(x_len, h_len) as hd:
+        v.batch_int16(hd, x16, hh, out=yh)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            v.batch_int16(hd, x16, hh, out=yh)
+        dt = (time.perf_counter() - t0) / steps
+    out["c4_int16_in"] = {"value": batch * out_len / dt / 1e9, "unit": "GSamples/s", "ms_per_step": 1e3 * dt,
+                          "h2d_bytes_per_step": 2 * batch * x_len + 4 * h_len, "d2h_bytes_per_step": 4 * batch * out_len,
+                          "pcie_bytes_per_output": (2 * batch * x_len + 4 * batch * out_len) / (batch * out_len),
+                          "call": "convolve_batch_int16 (int16 samples cross PCIe, widened on the device)",
+                          "replaces": "int16_to_float on the host + convolve_batch: 8 PCIe bytes per output"}
+    del x16, yh
+    # (2) correlate -> peaks
+    xl, hl = 2 ** 26, 512
+    xs = torch.empty((xl,), dtype=torch.float32).pin_memory()
+    t = torch.arange(xl, dtype=torch.float32)
+    xs.copy_(torch.sin(t * 0.001) + 0.25 * torch.sin(t * 0.0137) + 0.01 * torch.randn(xl))
+    del t
+    hs = torch.hann_window(hl).pin_memory()
+    pos, val = v.cross_correlate_peaks(xs, hs)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        pos, val = v.cross_correlate_peaks(xs, hs)
+    dt = (time.perf_counter() - t0) / steps
+    ys = torch.empty((xl + hl - 1,), dtype=torch.float32).pin_memory()
+    with v.Handle(xl, hl, "", True) as hd:
+        hd(xs, hs, out=ys)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            hd(xs, hs, out=ys)
+            pos2, val2 = v.detect_peaks(ys.numpy())
+        dt2 = (time.perf_counter() - t0) / steps
+    assert np.array_equal(pos, pos2) and np.array_equal(val, val2)
+    out["correlate_peaks_only"] = {
+        "value": (xl + hl - 1) / dt / 1e9, "unit": "GSamples/s (correlation samples examined)", "ms_per_step": 1e3 * dt,
+        "h2d_bytes_per_step": 4 * (xl + hl), "d2h_bytes_per_step": 8 * int(pos.size), "extrema": int(pos.size),
+        "pcie_bytes_per_output": (4 * (xl + hl) + 8 * int(pos.size)) / (xl + hl - 1),
+        "call": "simd_b200_cross_correlate_peaks (the correlation stays in HBM, {position, value} pairs come back)",
+        "two_call_chain": {"value": (xl + hl - 1) / dt2 / 1e9, "ms_per_step": 1e3 * dt2,
+                           "what": "cross_correlate to host memory, then detect_peaks on that host array "
+                                   "(result down, result up again, peaks down): same extrema"}}
+    return out
+
+
 def e2e_single_process(c, name, steps):
     """Rank 0 alone: the whole batch in host memory through one convolve_batch call that spreads
     it over all the GPUs of the box (simd_b200_use_devices), other ranks idle."""
@@ -588,6 +646,11 @@ def main():
                     configs[name] = bench_config(c, name, st, args.warmup, e2e_steps=2, do_e2e=not args.no_e2e)
             except Exception as e:          # one config must not take the headline down
                 configs[name] = {"error": f"{type(e).__name__}: {e}"}
+    if all_configs and world == 1 and not args.no_e2e:
+        try:
+            configs.update(e2e_fewer_bytes(c))
+        except Exception as e:
+            configs["fewer_bytes"] = {"error": f"{type(e).__name__}: {e}"}
     single = None
     if world > 1 and not args.no_e2e and WORKLOADS[args.workload][1] > 1:
         barrier()
@@ -604,7 +667,7 @@ def main():
         base["fft_note"] = fft_standin_note()
         if all_configs:
             for name in configs:
-                if "error" not in configs[name]:
+                if name in WORKLOADS and "error" not in configs[name]:
                     b, _, _ = cpu_baseline(name, target_s=1.0)
                     configs[name]["cpu_baseline"] = b
 
