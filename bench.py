@@ -653,13 +653,16 @@ def main():
             configs["fewer_bytes"] = {"error": f"{type(e).__name__}: {e}"}
     single = None
     if world > 1 and not args.no_e2e and WORKLOADS[args.workload][1] > 1:
+        # the other ranks must leave their GPUs idle while rank 0 drives all of them: wait on a
+        # CPU (gloo) barrier -- an NCCL barrier is a kernel spinning on every waiting GPU
+        cpu_group = dist.new_group(backend="gloo")
         barrier()
         if rank == 0:
             try:
                 single = e2e_single_process(c, args.workload, args.e2e_steps)
             except Exception as e:
                 single = {"error": f"{type(e).__name__}: {e}"}
-        barrier()
+        dist.barrier(group=cpu_group)
 
     base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

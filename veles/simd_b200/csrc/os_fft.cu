@@ -622,7 +622,9 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
                                   // (later pairs: the barriers of the previous pair do this)
   unsigned parity = 0;
   bool store_pending = false;     // a bulk store is still reading staged results from `sm`
-  asm volatile("griddepcontrol.wait;" ::: "memory");     // the spectrum kernel is short
+  // the spectrum kernel is short; waiting for it here rather than at the first centre pass keeps
+  // the statement out of the loop (inside it measured 2.7 % on C4)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   for (; item < p.total; item += gridDim.x) {
     {
       SegPair w;
@@ -705,6 +707,209 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
     }
   }
   // staged results must be out of shared memory before the CTA retires
+  if (t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  tmem::fence_before_sync();
+  __syncthreads();
+  if (t < 32) tmem::free_all(*tmem_base);
+}
+
+// ---- persistent variant of the real-packed kernel (N = 16384: one real segment of 32768
+// samples per transform; config C5's h = 8192) ------------------------------------------------
+// Same recipe as the paired persistent kernel where it applies:
+//  * twiddle factors in Tensor Memory, filled once per CTA;
+//  * the {alpha, beta} coefficients of the first kResRows centre registers (80 of their 256 KiB)
+//    are copied into the shared memory beside the transform buffer once per CTA and read from
+//    there for every segment; the rest still comes from L2;
+//  * results leave through shared memory and one bulk store per segment.
+// Input rows are 8-byte global loads as in the plain kernel (a segment's 128 KiB do not fit
+// beside the transform buffer), with the next segment prefetched into L2.
+constexpr int kResRows = 5;             // of 16 centre registers: 5 x 16 KiB resident
+
+template <class P>
+__device__ __forceinline__ void fwd_first_real_tm(int t, const SegReal &w, float2 *sm, unsigned tw_addr,
+                                                  bool wait_store) {
+  constexpr int R = P::R1, NB = P::N;
+  static_assert(R == 32 && P::E == R, "one radix-32 butterfly per thread");
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate(t, 0, base, npp, bf);
+  auto *smb = sm + pad_pos(base);
+  float2 v[R];
+  tmem::Chunk a, b;
+  tmem::load(a, tw_addr);
+  tmem::load(b, tw_addr + 16);
+  const bool inside = w.in0 >= 0 && w.in0 + 2 * P::N <= w.x_len;                   // CTA-uniform
+  const bool fast = inside && (((unsigned long long)(w.x + w.in0)) & 7ull) == 0;   // 8-byte loads
+  if (fast) {
+    const float2 *xa = reinterpret_cast<const float2 *>(w.x + w.in0) + base;
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = xa[r * G::S];
+    });
+  } else if (inside) {
+    const float *xa = w.x + (w.in0 + 2 * (i64)base);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = make_float2(xa[2 * r * G::S], xa[2 * r * G::S + 1]);
+    });
+  } else {
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const i64 i = w.in0 + 2 * (i64)(base + r * G::S);
+      v[bitrev(r, ilog2(R))] = make_float2(load_x(w.x, w.x_len, i), load_x(w.x, w.x_len, i + 1));
+    });
+  }
+  dft_inreg<R, false>(v);
+  tm_twiddle_fwd(v, tw_addr, a, b);
+  if (wait_store) wait_staged_results_read(t);      // CTA-uniform
+  static_for<0, R>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    smb[G::off(k)] = v[k];
+  });
+}
+
+// centre, step 2 with the first kResRows coefficient rows in shared memory:
+// ABs[(j * kResRows + k) * T + t] = AB[(k * T + t) * JB + j] for k < kResRows
+template <class P>
+__device__ __forceinline__ void centre_real_mix_res(int t, const float4 *AB, const float4 *ABs,
+                                                    const float2 *sm, float2 *u) {
+  constexpr int R = P::R3, JB = P::E / R;
+  static_for<0, JB>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    const float2 *smb = sm + pad_pos(base);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      const float2 z = smb[k];
+      const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k))];
+      float4 ab;
+      if constexpr (k < kResRows) ab = ABs[(j * kResRows + k) * P::T + t];
+      else ab = AB[(size_t)(k * P::T + t) * JB + j];
+      float2 r = cmul(z, make_float2(ab.x, ab.y));
+      r.x = fmaf(ab.z, zm.x, fmaf(ab.w, zm.y, r.x));          // + beta * conj(zm)
+      r.y = fmaf(ab.w, zm.x, fmaf(-ab.z, zm.y, r.y));
+      u[j * R + bitrev(k, ilog2(R))] = r;
+    });
+    dft_inreg<R, true>(u + j * R);
+  });
+}
+
+// last pass -> registers: register r holds circular samples 2p and 2p+1, p = base + r*S
+template <class P>
+__device__ __forceinline__ void inv_last_real_regs_tm(int t, const float2 *sm, float2 *v, unsigned tw_addr) {
+  constexpr int R = P::R1, NB = P::N;
+  using G = PassGeom<P, NB, R>;
+  int base, npp, bf;
+  G::locate(t, 0, base, npp, bf);
+  tm_load_twiddled_inv<P, G, R>(sm + pad_pos(base), v, tw_addr);
+  dft_inreg<R, true>(v);
+}
+
+template <class P>
+__global__ void __launch_bounds__(P::T) os_fused_real_persist_kernel(OsParams p) {
+  extern __shared__ float4 smem4[];
+  float2 *sm = reinterpret_cast<float2 *>(smem4);
+  float4 *ABs = reinterpret_cast<float4 *>(sm + P::SMEM_FLOAT2);                 // 2 * kResRows * T
+  unsigned *tmem_base = reinterpret_cast<unsigned *>(ABs + 2 * kResRows * P::T);
+  const int t = threadIdx.x;
+  constexpr int R = P::R1;
+  using G = PassGeom<P, P::N, R>;
+
+  if (t < 32) tmem::alloc_all(tmem_base);
+  tmem::fence_before_sync();
+  __syncthreads();
+  tmem::fence_after_sync();
+  const unsigned tw_addr = tmem::thread_base(*tmem_base, t);
+  tm_fill_twiddles<P>(t, p.tw, tw_addr);
+
+  auto seg_of = [&](i64 item, SegReal &w) {
+    const i64 b = item / p.nseg;
+    const i64 sg = item % p.nseg;
+    w.x = p.x + b * p.x_stride;
+    w.x_len = p.x_len;
+    w.in0 = sg * p.step + p.in_shift;
+    w.out = p.out + b * p.out_stride;
+    w.out0 = sg * p.step;
+    const i64 rem = p.out_len - w.out0;
+    w.cnt = (int)(rem < p.step ? rem : p.step);
+    w.c_off = p.c_off;
+    w.accumulate = false;
+  };
+  auto prefetch = [&](i64 item) {                 // one thread: next segment's input into L2
+    if (item >= p.total) return;
+    SegReal w;
+    seg_of(item, w);
+    i64 lo = w.in0 < 0 ? 0 : w.in0;
+    i64 hi = w.in0 + 2 * P::N;
+    if (hi > w.x_len) hi = w.x_len;
+    const unsigned long long a0 = ((unsigned long long)(w.x + lo) + 15ull) & ~15ull;
+    const unsigned long long a1 = (unsigned long long)(w.x + hi) & ~15ull;
+    if (a1 > a0)
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a0), "r"((unsigned)(a1 - a0)) : "memory");
+  };
+
+  // the coefficient kernel runs ahead of us (programmatic dependent launch)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const float4 *AB = reinterpret_cast<const float4 *>(p.spectrum);
+  for (int i = t; i < 2 * kResRows * P::T; i += P::T) {
+    const int j = i / (kResRows * P::T), k = (i / P::T) % kResRows, tt = i % P::T;
+    ABs[i] = AB[(size_t)(k * P::T + tt) * 2 + j];
+  }
+  __syncthreads();
+
+  bool store_pending = false;
+  for (i64 item = blockIdx.x; item < p.total; item += gridDim.x) {
+    SegReal w;
+    seg_of(item, w);
+    if (t == 0) prefetch(item + gridDim.x);
+    fwd_first_real_tm<P>(t, w, sm, tw_addr, store_pending);
+    store_pending = false;
+    __syncthreads();
+    fwd_mid_tm<P>(t, sm, tw_addr);
+    __syncwarp();                       // middle passes stay inside the half-warp
+    centre_real_fwd<P>(t, sm);
+    __syncthreads();                    // mirror bins live in other threads
+    float2 u[P::E];
+    centre_real_mix_res<P>(t, AB, ABs, sm, u);
+    __syncthreads();                    // every mirror has been read: safe to overwrite
+    centre_real_store<P>(t, sm, u);
+    __syncwarp();
+    inv_mid_tm<P>(t, sm, tw_addr);
+    __syncthreads();
+    inv_last_real_regs_tm<P>(t, sm, u, tw_addr);
+    // results -> shared memory (stage[phase + tt], shared and global addresses congruent
+    // mod 16 bytes) -> one bulk store; c_off is even, so a register's two samples are a pair
+    float *st = reinterpret_cast<float *>(sm);
+    const int phase = (int)((((unsigned long long)(w.out + w.out0)) >> 2) & 3ull);
+    int base, npp, bf;
+    G::locate(t, 0, base, npp, bf);
+    __syncthreads();                    // every thread has read its last-pass inputs
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const unsigned tt = (unsigned)(2 * (base + r * G::S) - w.c_off);      // negative -> huge
+      if (tt < (unsigned)p.step) {
+        st[phase + tt] = u[r].x;
+        st[phase + tt + 1] = u[r].y;
+      }
+    });
+    __syncthreads();
+    const int head = (4 - phase) & 3;
+    const int mid = w.cnt > head ? (w.cnt - head) & ~3 : 0;
+    float *g = w.out + w.out0;
+    if (t < 8) {
+      const int k = t < 4 ? t : head + mid + (t - 4);
+      if ((t < 4 ? k < head : true) && k < w.cnt) g[k] = st[phase + k];
+    }
+    if (t == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      if (mid > 0)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g + head),
+                     "r"(smem_u32(st + phase + head)), "r"((unsigned)mid * 4u) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    store_pending = true;
+  }
   if (t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tmem::fence_before_sync();
   __syncthreads();
@@ -955,6 +1160,39 @@ void b200_os_launch_real(const float2 *tw, float4 *coeffs, int n_fft, const DevJ
   op.npairs = op.nseg;
   op.total = op.nseg * job.batch;
 
+  if (n_fft == 16384 && !getenv("VELES_B200_NO_PERSIST")) {
+    using PLAN = P16384;
+    static bool configured[16] = {false};
+    static int sms[16] = {0};
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    const size_t smem = sizeof(float2) * PLAN::SMEM_FLOAT2 + sizeof(float4) * 2 * kResRows * PLAN::T + 16;
+    if (dev < 16 && op.total < 2147483647LL) {
+      if (!configured[dev]) {
+        B200_CUDA_CHECK(cudaFuncSetAttribute(os_fused_real_persist_kernel<PLAN>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA_CHECK(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
+        configured[dev] = true;
+      }
+      launch_spectrum<PLAN, true>(sp, 1, stream);
+      const i64 blocks = op.total < sms[dev] ? op.total : sms[dev];
+      b200_prof_begin(B200_PROF_FUSED, stream);
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)blocks);
+      cfg.blockDim = dim3(PLAN::T);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, os_fused_real_persist_kernel<PLAN>, op));
+      b200_prof_end(B200_PROF_FUSED, stream);
+      b200_count_launch(1);
+      return;
+    }
+  }
 #define B200_DISPATCH_REAL(PLAN, GROUPS)                       \
   case PLAN::N:                                                \
     launch_spectrum<PLAN, true>(sp, 1, stream);                \
