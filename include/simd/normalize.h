@@ -14,7 +14,10 @@ SIMD_API_BEGIN
 
 /* Replaces reference inc/simd/normalize.h:81-90 / src/normalize.c:323-380,425-443,503-521.
  * Minimum and maximum of src[0..length); either result pointer may be NULL (then that value
- * is not produced).  src: host or device pointer, length > 0; min / max: host pointers. */
+ * is not produced).  src: host or device pointer, length > 0; min / max: host pointers.
+ * NaN samples are ignored (fminf / fmaxf), as the reference's scalar loop ignores them through
+ * its `<` / `>` updates -- except that the reference returns NaN when src[0] itself is NaN
+ * (it starts from src[0]); here a leading NaN is ignored like any other. */
 void minmax1D(int simd, const float *src, int length, float *min, float *max) NOTNULL(2);
 
 /* Additive: device-resident and asynchronous on the library stream.  d_minmax[0] = minimum,

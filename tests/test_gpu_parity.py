@@ -550,6 +550,19 @@ def test_minmax1D_parity(simd, oracle):
         simd.lib.simd_b200_minmax1D_device(xd.data_ptr(), n, out.data_ptr())
         torch.cuda.synchronize()
         assert tuple(out.cpu().tolist()) == want
+    # NaN samples.  The reference's scalar loop (src/normalize.c:425-443) starts from src[0] and
+    # updates with `<` / `>`, so NaNs after the first sample never win a comparison: they are
+    # ignored -- and so they are here (fminf / fmaxf), for any position but the first.  A NaN in
+    # src[0] makes the reference return NaN for both; here it is ignored like any other (pinned
+    # below: the one documented difference, include/simd/normalize.h).
+    x = rng.standard_normal(100001).astype(np.float32)
+    x[[7, 5000, 99999]] = np.nan
+    want = oracle.minmax1D(x)
+    assert not np.isnan(want).any()
+    assert simd.minmax1D(x) == want
+    assert simd.minmax1D(torch.from_numpy(x).cuda()) == want
+    x[0] = np.nan
+    assert simd.minmax1D(x) == (float(np.nanmin(x)), float(np.nanmax(x)))
 
 
 def test_int16_converters_parity(simd, oracle):
