@@ -18,10 +18,11 @@ batched C-ABI entry point (convolve_batch) of libSimd.so.
 
 Workloads (BASELINE.json configs): c4 is the headline (batched FFT/overlap-save regime, the
 largest batched configuration); with no --workload the line also carries a `configs` object
-with c1, c2, c3 and c5.  Under torchrun (N > 1) the batched configs are split by rows over
-the ranks (BASELINE: "sharded by batch"; total work fixed: strong scaling, no data-path
-collective), c5 is sharded contiguously with its (h-1)-sample halo exchanged point to point,
-c1/c2 run as replicas.
+with c1, c2, c3 and c5.  Under torchrun (N > 1) the headline runs the whole config on every
+rank's GPU (weak scaling, no data-path collective) and configs.c4_strong the same config split
+by rows over the ranks (BASELINE: "sharded by batch"; total work fixed: strong scaling), as is
+c3; c5 is sharded contiguously with its (h-1)-sample halo exchanged point to point; c1/c2 run
+as replicas.
 """
 import argparse
 import json
@@ -221,15 +222,20 @@ class Ctx:
 
 
 def bench_config(c, name, steps, warmup, min_warm_s=0.0, e2e_steps=3, do_e2e=True, do_pageable=False,
-                 algorithm=-1, no_profile=False, out_row_align=1):
+                 algorithm=-1, no_profile=False, out_row_align=1, weak=False):
     """One BASELINE config on this rank's share of it.  Batched configs are split by rows over
-    the ranks (strong scaling: the batch is fixed); single-signal configs run as replicas."""
+    the ranks (strong scaling: the batch is fixed) -- or, with weak=True, every rank runs the
+    whole batch of the config on its own GPU (weak scaling: work grows with the ranks);
+    single-signal configs run as replicas."""
     torch, dist, v = c.torch, c.dist, c.v
     op, batch, x_len, h_len, desc = WORKLOADS[name]
     corr = op == "correlate"
     out_len = x_len + h_len - 1
     from veles.simd_b200 import sharded
-    if batch > 1:
+    if batch > 1 and weak and c.world > 1:
+        lo, hi = 0, batch
+        sharding = f"every rank runs all {batch} signals of the config on its own GPU, no collective"
+    elif batch > 1:
         lo, hi = sharded.batch_rows(batch, c.rank, c.world)
         sharding = f"rows [{lo},{hi}) of {batch} on this rank, no collective" if c.world > 1 else "one GPU"
     else:
@@ -303,7 +309,7 @@ def bench_config(c, name, steps, warmup, min_warm_s=0.0, e2e_steps=3, do_e2e=Tru
         v.profile(False)
     step_ms = [a.elapsed_time(b) for a, b in ev]
     ms_per_step = c.max_over_ranks(sum(step_ms)) / steps
-    replicas = c.world if batch == 1 else 1
+    replicas = c.world if (batch == 1 or (weak and c.world > 1)) else 1
     outputs_per_step = batch * out_len * replicas
     value = outputs_per_step / (ms_per_step * 1e-3) / 1e9
 
@@ -370,8 +376,8 @@ def bench_config(c, name, steps, warmup, min_warm_s=0.0, e2e_steps=3, do_e2e=Tru
             handle(xh, hh, out=yh)        # returns with the result in host memory
         dt = c.max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": outputs_per_step * reps / dt / 1e9, "unit": "GSamples/s",
-               "h2d_bytes_per_step": 4 * (nb * x_len + h_len) * (c.world if batch > 1 else replicas),
-               "d2h_bytes_per_step": 4 * nb * out_len * (c.world if batch > 1 else replicas),
+               "h2d_bytes_per_step": 4 * (nb * x_len + h_len) * c.world,
+               "d2h_bytes_per_step": 4 * nb * out_len * c.world,
                "steps": reps, "ms_per_step": 1e3 * dt / reps, "host_memory": "pinned",
                "result_checksum": float(yh.reshape(-1)[:1024].double().sum())}
         if batch == 1 and x_len < 1 << 20:
@@ -401,7 +407,8 @@ def bench_config(c, name, steps, warmup, min_warm_s=0.0, e2e_steps=3, do_e2e=Tru
            "workload": f"{name}: {desc}", "op": op, "signals_total": batch, "signals_this_rank": nb,
            "x_length": x_len, "h_length": h_len,
            "algorithm": {0: "direct", 1: "fft", 2: "overlap_save"}[alg], "transform_length": n_fft,
-           "scaling": "strong" if batch > 1 else "replicas", "sharding": sharding,
+           "scaling": ("weak" if weak else "strong") if batch > 1 else "replicas",
+           "sharding": sharding,
            "l2": ("inputs larger than L2" if flush is None else "256 MiB flush buffer written between steps"),
            "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
            "step_ms": {"min": min(step_ms), "max": max(step_ms)}}
@@ -562,6 +569,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="headline only")
+    ap.add_argument("--strong", action="store_true",
+                    help="N > 1: split the headline config's batch by rows instead of one whole batch per rank")
     ap.add_argument("--out-row-align", type=int, default=1,
                     help="pad result rows to a multiple of this many floats (experiment)")
     ap.add_argument("--no-profile", action="store_true",
@@ -627,13 +636,20 @@ def main():
     if args.workload == "c5" and world > 1:
         head = bench_c5_sharded(c, args.steps, args.warmup)
     else:
+        # headline at N > 1: every rank the whole config on its own GPU (weak scaling, as in round
+        # 1); the same config split by rows (strong scaling, BASELINE's "sharded by batch") is in
+        # configs.<name>_strong right beside it
         head = bench_config(c, args.workload, args.steps, args.warmup, min_warm_s=args.min_warm_s,
-                            e2e_steps=args.e2e_steps, do_e2e=not args.no_e2e, do_pageable=not args.no_e2e,
+                            e2e_steps=args.e2e_steps, do_e2e=not args.no_e2e,
+                            do_pageable=not args.no_e2e and world == 1,
                             algorithm=args.algorithm, no_profile=args.no_profile,
-                            out_row_align=args.out_row_align)
+                            out_row_align=args.out_row_align, weak=not args.strong)
     clocks = sampler.stop() if rank == 0 else None
 
     configs = {}
+    if world > 1 and WORKLOADS[args.workload][1] > 1 and not args.strong and not args.no_configs:
+        configs[args.workload + "_strong"] = bench_config(c, args.workload, args.steps, args.warmup,
+                                                          e2e_steps=2, do_e2e=not args.no_e2e)
     if all_configs:
         # every other BASELINE config, fewer steps each; at N > 1 the batched ones are split by
         # rows (strong scaling), C5 is sharded with its halo, C1/C2 run as replicas
