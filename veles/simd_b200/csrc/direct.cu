@@ -47,12 +47,20 @@ struct DirectParams {
   int reverse;
   int hc_max;           // taps per staging pass (multiple of 16)
   int xbuf_floats;      // size of one padded x buffer
+  int lead;             // pipelined kernel: tile t covers outputs [t*kTile - lead, ...): chosen so that
+                        // every tile's x window starts on a 16-byte boundary (0..3)
+  int wide;             // ... and is then staged with 16-byte cp.async
 };
 
 __device__ __forceinline__ void cp_async4(float *smem_dst, const float *gsrc, bool valid) {
   unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   int sz = valid ? 4 : 0;      // src-size 0 -> the 4 destination bytes are zero-filled
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz));
+}
+// 16 bytes; `bytes` of them (0, 4, 8, 12 or 16) come from global memory, the rest is zero-filled
+__device__ __forceinline__ void cp_async16(float *smem_dst, const float *gsrc, int bytes) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gsrc), "r"(bytes));
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
@@ -131,7 +139,21 @@ __global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
   const int t0 = tid * kR;
 
   auto stage = [&](i64 tile, float *xs) {
-    const i64 xi0 = tile * kTile - p.pad;
+    const i64 xi0 = tile * kTile - p.lead - p.pad;
+    if (p.wide) {
+      // xi0 is a multiple of 4 and the row starts on a 16-byte boundary: whole 16-byte units,
+      // four samples each, never straddling a 16-sample padded row; a unit is inside the signal,
+      // outside it (zero-filled), or -- at the signal's end only -- partly inside
+      const int units = (wlen + 3) >> 2;
+      for (int u = tid; u < units; u += kTPB) {
+        const i64 i = xi0 + 4 * (i64)u;
+        const i64 left = p.x_len - i;                      // samples of the signal from i on
+        const int n = i < 0 || left <= 0 ? 0 : (left < 4 ? (int)left : 4);
+        cp_async16(xs + padx(4 * u), n ? xb + i : xb, 4 * n);
+      }
+      cp_async_commit();
+      return;
+    }
     const float *s = xb + xi0 + tid;
     // q advances by kTPB = 128 (a multiple of the 16-float row), so the padded address
     // advances by a constant 128 + 32 floats: no per-element index arithmetic
@@ -162,7 +184,7 @@ __global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
                                            // the other buffer is no longer being read
     if (tile + 1 < tile_end) stage(tile + 1, xbuf0 + (buf ^ 1) * p.xbuf_floats);
 
-    const i64 n0 = tile * kTile;
+    const i64 n0 = tile * kTile - p.lead;              // first output of the tile (tile 0: may be < 0)
     const i64 remaining = p.out_len - n0;
     const int cnt = remaining < kTile ? (int)remaining : kTile;
     const bool active = ((tid & ~31) * kR) < cnt;    // warp-uniform
@@ -185,8 +207,14 @@ __global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
     float *o = ob + n0 + tid;
     const float *sr = obuf + padx(tid);
     const int oiters = (cnt - tid + kTPB - 1) / kTPB;
+    if (n0 >= 0) {
 #pragma unroll 4
-    for (int k = 0; k < oiters; k++, o += kTPB, sr += kTPB + kTPB / 4) *o = *sr;
+      for (int k = 0; k < oiters; k++, o += kTPB, sr += kTPB + kTPB / 4) *o = *sr;
+    } else {
+      // tile 0 of a signal whose tiles were shifted for alignment: its first `lead` outputs do not exist
+      for (int k = 0; k < oiters; k++, o += kTPB, sr += kTPB + kTPB / 4)
+        if (n0 + tid + (i64)k * kTPB >= 0) *o = *sr;
+    }
   }
 }
 
@@ -317,6 +345,7 @@ void b200_direct_launch(const DevJob &job, cudaStream_t stream) {
   p.h = job.h; p.h_len = job.h_len;
   p.out = job.out; p.out_len = job.out_len; p.out_stride = job.out_stride;
   p.pad = job.pad; p.reverse = job.reverse;
+  p.lead = 0; p.wide = 0;
   p.tiles_per_signal = (job.out_len + kTile - 1) / kTile;
   i64 hc = job.h_len < kMaxHC ? job.h_len : kMaxHC;
   p.hc_max = (int)((hc + 15) & ~15LL);
@@ -338,6 +367,13 @@ void b200_direct_launch(const DevJob &job, cudaStream_t stream) {
     i64 strip = tiles / (148 * 10);
     if (strip < 1) strip = 1;
     if (strip > kMaxStrip) strip = kMaxStrip;
+    if (strip > p.tiles_per_signal) strip = p.tiles_per_signal;
+    // shift the tiles so that each one's x window starts 16-byte aligned in global memory; then
+    // it is staged in 16-byte units (needs rows that start on 16-byte boundaries themselves)
+    p.wide = ((((unsigned long long)job.x) & 15ull) == 0 && (job.x_stride & 3) == 0 &&
+              !getenv("VELES_B200_DIRECT_NARROW")) ? 1 : 0;
+    p.lead = p.wide ? (int)(((-job.pad) % 4 + 4) % 4) : 0;
+    p.tiles_per_signal = (job.out_len + p.lead + kTile - 1) / kTile;
     if (strip > p.tiles_per_signal) strip = p.tiles_per_signal;
     p.strip = (int)strip;
     p.strips_per_signal = (p.tiles_per_signal + strip - 1) / strip;
