@@ -715,19 +715,17 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
 
 // ---- persistent variant of the real-packed kernel (N = 16384: one real segment of 32768
 // samples per transform; config C5's h = 8192) ------------------------------------------------
-// Same recipe as the paired persistent kernel where it applies:
-//  * twiddle factors in Tensor Memory, filled once per CTA;
-//  * the {alpha, beta} coefficients of the first kResRows centre registers (80 of their 256 KiB)
-//    are copied into the shared memory beside the transform buffer once per CTA and read from
-//    there for every segment; the rest still comes from L2;
-//  * results leave through shared memory and one bulk store per segment.
-// Input rows are 8-byte global loads as in the plain kernel (a segment's 128 KiB do not fit
-// beside the transform buffer), with the next segment prefetched into L2.
-constexpr int kResRows = 5;             // of 16 centre registers: 5 x 16 KiB resident
-
+// One CTA per SM loops over segments with its twiddle factors in Tensor Memory (filled once per
+// CTA), the next segment's input prefetched into L2.  Everything else is the plain kernel's:
+// 8-byte global loads of the input rows, {alpha, beta} from L2, 8-byte global stores of the
+// results.  This kernel is bound by the shared-memory instruction queue (`mio_throttle` is its
+// largest stall), so what helped the paired kernel hurts here -- measured on one GPU, C5:
+//   plain kernel 4.670 ms | + Tensor-Memory twiddles, persistent 4.256 | + results staged in
+//   shared memory and bulk-stored 4.504 | + the first 5 of 16 {alpha, beta} rows resident in
+//   shared memory 4.438 | both 4.583.
 template <class P>
 __device__ __forceinline__ void fwd_first_real_tm(int t, const SegReal &w, float2 *sm, unsigned tw_addr,
-                                                  bool wait_store) {
+                                                  bool buffer_in_use) {
   constexpr int R = P::R1, NB = P::N;
   static_assert(R == 32 && P::E == R, "one radix-32 butterfly per thread");
   using G = PassGeom<P, NB, R>;
@@ -761,37 +759,12 @@ __device__ __forceinline__ void fwd_first_real_tm(int t, const SegReal &w, float
   }
   dft_inreg<R, false>(v);
   tm_twiddle_fwd(v, tw_addr, a, b);
-  if (wait_store) wait_staged_results_read(t);      // CTA-uniform
+  // the previous segment's last pass may still be reading the transform buffer in other threads:
+  // wait here, after this segment's loads and first butterflies, not before them (CTA-uniform)
+  if (buffer_in_use) __syncthreads();
   static_for<0, R>([&](auto kk) {
     constexpr int k = decltype(kk)::value;
     smb[G::off(k)] = v[k];
-  });
-}
-
-// centre, step 2 with the first kResRows coefficient rows in shared memory:
-// ABs[(j * kResRows + k) * T + t] = AB[(k * T + t) * JB + j] for k < kResRows
-template <class P>
-__device__ __forceinline__ void centre_real_mix_res(int t, const float4 *AB, const float4 *ABs,
-                                                    const float2 *sm, float2 *u) {
-  constexpr int R = P::R3, JB = P::E / R;
-  static_for<0, JB>([&](auto jj) {
-    constexpr int j = decltype(jj)::value;
-    int base, bf, k1, k2;
-    centre_locate<P>(t, j, base, bf, k1, k2);
-    const float2 *smb = sm + pad_pos(base);
-    static_for<0, R>([&](auto kk) {
-      constexpr int k = decltype(kk)::value;
-      const float2 z = smb[k];
-      const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k))];
-      float4 ab;
-      if constexpr (k < kResRows) ab = ABs[(j * kResRows + k) * P::T + t];
-      else ab = AB[(size_t)(k * P::T + t) * JB + j];
-      float2 r = cmul(z, make_float2(ab.x, ab.y));
-      r.x = fmaf(ab.z, zm.x, fmaf(ab.w, zm.y, r.x));          // + beta * conj(zm)
-      r.y = fmaf(ab.w, zm.x, fmaf(-ab.z, zm.y, r.y));
-      u[j * R + bitrev(k, ilog2(R))] = r;
-    });
-    dft_inreg<R, true>(u + j * R);
   });
 }
 
@@ -810,8 +783,7 @@ template <class P>
 __global__ void __launch_bounds__(P::T) os_fused_real_persist_kernel(OsParams p) {
   extern __shared__ float4 smem4[];
   float2 *sm = reinterpret_cast<float2 *>(smem4);
-  float4 *ABs = reinterpret_cast<float4 *>(sm + P::SMEM_FLOAT2);                 // 2 * kResRows * T
-  unsigned *tmem_base = reinterpret_cast<unsigned *>(ABs + 2 * kResRows * P::T);
+  unsigned *tmem_base = reinterpret_cast<unsigned *>(sm + P::SMEM_FLOAT2);
   const int t = threadIdx.x;
   constexpr int R = P::R1;
   using G = PassGeom<P, P::N, R>;
@@ -852,65 +824,46 @@ __global__ void __launch_bounds__(P::T) os_fused_real_persist_kernel(OsParams p)
   // the coefficient kernel runs ahead of us (programmatic dependent launch)
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const float4 *AB = reinterpret_cast<const float4 *>(p.spectrum);
-  for (int i = t; i < 2 * kResRows * P::T; i += P::T) {
-    const int j = i / (kResRows * P::T), k = (i / P::T) % kResRows, tt = i % P::T;
-    ABs[i] = AB[(size_t)(k * P::T + tt) * 2 + j];
-  }
-  __syncthreads();
 
-  bool store_pending = false;
   for (i64 item = blockIdx.x; item < p.total; item += gridDim.x) {
     SegReal w;
     seg_of(item, w);
     if (t == 0) prefetch(item + gridDim.x);
-    fwd_first_real_tm<P>(t, w, sm, tw_addr, store_pending);
-    store_pending = false;
+    fwd_first_real_tm<P>(t, w, sm, tw_addr, item != blockIdx.x);
     __syncthreads();
     fwd_mid_tm<P>(t, sm, tw_addr);
     __syncwarp();                       // middle passes stay inside the half-warp
     centre_real_fwd<P>(t, sm);
     __syncthreads();                    // mirror bins live in other threads
     float2 u[P::E];
-    centre_real_mix_res<P>(t, AB, ABs, sm, u);
+    centre_real_mix<P>(t, AB, sm, u);
     __syncthreads();                    // every mirror has been read: safe to overwrite
     centre_real_store<P>(t, sm, u);
     __syncwarp();
     inv_mid_tm<P>(t, sm, tw_addr);
     __syncthreads();
     inv_last_real_regs_tm<P>(t, sm, u, tw_addr);
-    // results -> shared memory (stage[phase + tt], shared and global addresses congruent
-    // mod 16 bytes) -> one bulk store; c_off is even, so a register's two samples are a pair
-    float *st = reinterpret_cast<float *>(sm);
-    const int phase = (int)((((unsigned long long)(w.out + w.out0)) >> 2) & 3ull);
+    // register r holds circular samples 2p and 2p+1, p = base + r*S: c_off is even, so they are
+    // a pair of outputs -- one 8-byte store when the result row allows it
     int base, npp, bf;
     G::locate(t, 0, base, npp, bf);
-    __syncthreads();                    // every thread has read its last-pass inputs
-    static_for<0, R>([&](auto rr) {
-      constexpr int r = decltype(rr)::value;
-      const unsigned tt = (unsigned)(2 * (base + r * G::S) - w.c_off);      // negative -> huge
-      if (tt < (unsigned)p.step) {
-        st[phase + tt] = u[r].x;
-        st[phase + tt + 1] = u[r].y;
-      }
-    });
-    __syncthreads();
-    const int head = (4 - phase) & 3;
-    const int mid = w.cnt > head ? (w.cnt - head) & ~3 : 0;
-    float *g = w.out + w.out0;
-    if (t < 8) {
-      const int k = t < 4 ? t : head + mid + (t - 4);
-      if ((t < 4 ? k < head : true) && k < w.cnt) g[k] = st[phase + k];
+    float *o = w.out + (w.out0 + 2 * base - w.c_off);       // dereferenced only where 0 <= index < cnt
+    const bool pairs = (w.cnt & 1) == 0 && (((unsigned long long)(w.out + w.out0)) & 7ull) == 0;
+    if (pairs) {                        // CTA-uniform
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const unsigned tt = (unsigned)(2 * (base + r * G::S) - w.c_off);      // negative -> huge
+        if (tt < (unsigned)w.cnt) *reinterpret_cast<float2 *>(o + 2 * r * G::S) = u[r];
+      });
+    } else {
+      static_for<0, R>([&](auto rr) {
+        constexpr int r = decltype(rr)::value;
+        const unsigned tt = (unsigned)(2 * (base + r * G::S) - w.c_off);
+        if (tt < (unsigned)w.cnt) o[2 * r * G::S] = u[r].x;
+        if (tt + 1u < (unsigned)w.cnt) o[2 * r * G::S + 1] = u[r].y;
+      });
     }
-    if (t == 0) {
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      if (mid > 0)
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g + head),
-                     "r"(smem_u32(st + phase + head)), "r"((unsigned)mid * 4u) : "memory");
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    }
-    store_pending = true;
   }
-  if (t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tmem::fence_before_sync();
   __syncthreads();
   if (t < 32) tmem::free_all(*tmem_base);
@@ -1166,7 +1119,7 @@ void b200_os_launch_real(const float2 *tw, float4 *coeffs, int n_fft, const DevJ
     static int sms[16] = {0};
     int dev = 0;
     B200_CUDA_CHECK(cudaGetDevice(&dev));
-    const size_t smem = sizeof(float2) * PLAN::SMEM_FLOAT2 + sizeof(float4) * 2 * kResRows * PLAN::T + 16;
+    const size_t smem = sizeof(float2) * PLAN::SMEM_FLOAT2 + 16;
     if (dev < 16 && op.total < 2147483647LL) {
       if (!configured[dev]) {
         B200_CUDA_CHECK(cudaFuncSetAttribute(os_fused_real_persist_kernel<PLAN>,
