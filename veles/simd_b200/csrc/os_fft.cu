@@ -398,13 +398,21 @@ __device__ __forceinline__ void fwd_first_tm(int t, const SegPair &w, float2 *sm
   tmem::Chunk a, b;
   tmem::load(a, tw_addr);
   tmem::load(b, tw_addr + 16);
-  static_for<0, R>([&](auto rr) {
-    constexpr int r = decltype(rr)::value;
-    const int p = base + r * G::S;
-    const float va = load_x(w.x, w.x_len, w.inA + p);
-    const float vb = w.haveB ? load_x(w.x, w.x_len, w.inB + p) : 0.0f;
-    v[bitrev(r, ilog2(R))] = make_float2(va, vb);
-  });
+  if (w.haveB && w.inA >= 0 && w.inB + P::N <= w.x_len) {      // CTA-uniform: no bounds checks
+    const float *xa = w.x + (w.inA + base), *xb = w.x + (w.inB + base);
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = make_float2(xa[r * G::S], xb[r * G::S]);
+    });
+  } else {
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      const int p = base + r * G::S;
+      const float va = load_x(w.x, w.x_len, w.inA + p);
+      const float vb = w.haveB ? load_x(w.x, w.x_len, w.inB + p) : 0.0f;
+      v[bitrev(r, ilog2(R))] = make_float2(va, vb);
+    });
+  }
   dft_inreg<R, false>(v);
   tm_twiddle_fwd(v, tw_addr, a, b);
   before_stores();
