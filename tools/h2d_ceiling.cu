@@ -95,7 +95,33 @@ int main() {
     t0 = now();
     for (int r = 0; r < 4; r++) memcpy(devs[0].h_in, p, kBytes);
     double mc = (double)kBytes * 4 / (now() - t0) / 1e9;
-    printf("],\n \"pageable_one_gpu\": {\"h2d_gbs\": %.1f, \"d2h_gbs\": %.1f, \"host_memcpy_to_pinned_gbs_one_thread\": %.1f}}\n", h2d, d2h, mc);
+    printf("],\n \"pageable_one_gpu\": {\"h2d_gbs\": %.1f, \"d2h_gbs\": %.1f, \"host_memcpy_to_pinned_gbs_one_thread\": %.1f", h2d, d2h, mc);
+    // the same copy split over several threads (what the library's bounce pipeline does), and
+    // both directions at once (pageable -> pinned and pinned -> pageable, half the threads each)
+    char *q = (char *)malloc(kBytes);
+    memset(q, 3, kBytes);
+    printf(", \"host_memcpy_threads\": [");
+    int counts[] = {2, 4, 8, 12, 16, 24, 32};
+    for (int ci = 0; ci < 7; ci++) {
+      int nt = counts[ci];
+      auto run_mt = [&](bool both) {
+        double t1 = now();
+        for (int r = 0; r < 4; r++) {
+          std::vector<std::thread> th;
+          for (int i = 0; i < nt; i++) th.emplace_back([&, i]() {
+            size_t per = kBytes / nt, off = per * i;
+            if (both && (i & 1)) memcpy(q + off, devs[0].h_out + off, per);
+            else memcpy(devs[0].h_in + off, p + off, per);
+          });
+          for (auto &t : th) t.join();
+        }
+        return (double)kBytes * 4 / (now() - t1) / 1e9;
+      };
+      double one = run_mt(false), two = run_mt(true);
+      printf("%s{\"threads\": %d, \"to_pinned_gbs\": %.1f, \"both_ways_total_gbs\": %.1f}", ci ? ", " : "", nt, one, two);
+    }
+    printf("]}}\n");
+    free(q);
     free(p);
   }
   return 0;

@@ -776,6 +776,58 @@ __device__ __forceinline__ void fwd_first_real_tm(int t, const SegReal &w, float
   });
 }
 
+// centre of the real-packed transform with this thread's own bins kept in registers across the
+// barrier (the plain kernel writes them to shared memory for the mirror reads of other threads
+// AND reads its own back afterwards: 32 shared-memory loads per thread that this form saves).
+// step 1: last forward pass; bins to shared memory (others read them as mirrors) and to z[]
+template <class P>
+__device__ __forceinline__ void centre_real_fwd_keep(int t, float2 *sm, float2 *z) {
+  constexpr int R = P::R3;
+  static_for<0, P::E / R>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    auto *smb = sm + pad_pos(base);
+    float2 *v = z + j * R;
+    static_for<0, R>([&](auto rr) {
+      constexpr int r = decltype(rr)::value;
+      v[bitrev(r, ilog2(R))] = smb[r];
+    });
+    dft_inreg<R, false>(v);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      smb[k] = v[k];
+    });
+  });
+}
+// step 2 (after a CTA barrier): Z' = alpha*Z + beta*conj(Z_mirror) in place, then the first
+// inverse pass; z[] holds the results in natural order afterwards
+template <class P>
+__device__ __forceinline__ void centre_real_mix_keep(int t, const float4 *AB, const float2 *sm, float2 *z) {
+  constexpr int R = P::R3, JB = P::E / R;
+  static_for<0, JB>([&](auto jj) {
+    constexpr int j = decltype(jj)::value;
+    int base, bf, k1, k2;
+    centre_locate<P>(t, j, base, bf, k1, k2);
+    float2 u[R];
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      const float2 own = z[j * R + k];
+      const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k))];
+      const float4 ab = AB[(size_t)(k * P::T + t) * JB + j];
+      float2 r = cmul(own, make_float2(ab.x, ab.y));
+      r.x = fmaf(ab.z, zm.x, fmaf(ab.w, zm.y, r.x));          // + beta * conj(zm)
+      r.y = fmaf(ab.w, zm.x, fmaf(-ab.z, zm.y, r.y));
+      u[bitrev(k, ilog2(R))] = r;
+    });
+    dft_inreg<R, true>(u);
+    static_for<0, R>([&](auto kk) {
+      constexpr int k = decltype(kk)::value;
+      z[j * R + k] = u[k];
+    });
+  });
+}
+
 // last pass -> registers: register r holds circular samples 2p and 2p+1, p = base + r*S
 template <class P>
 __device__ __forceinline__ void inv_last_real_regs_tm(int t, const float2 *sm, float2 *v, unsigned tw_addr) {
@@ -841,10 +893,10 @@ __global__ void __launch_bounds__(P::T) os_fused_real_persist_kernel(OsParams p)
     __syncthreads();
     fwd_mid_tm<P>(t, sm, tw_addr);
     __syncwarp();                       // middle passes stay inside the half-warp
-    centre_real_fwd<P>(t, sm);
-    __syncthreads();                    // mirror bins live in other threads
     float2 u[P::E];
-    centre_real_mix<P>(t, AB, sm, u);
+    centre_real_fwd_keep<P>(t, sm, u);
+    __syncthreads();                    // mirror bins live in other threads
+    centre_real_mix_keep<P>(t, AB, sm, u);
     __syncthreads();                    // every mirror has been read: safe to overwrite
     centre_real_store<P>(t, sm, u);
     __syncwarp();
