@@ -163,8 +163,8 @@ static int run_plan_real(const char *name, int h_len, int x_len, int reverse, in
     w.c_off = c_off; w.accumulate = false;
     for (int t = 0; t < P::T; t++) fwd_first_real<P>(t, w, tb[t], sm.data());
     if constexpr (P::NPASS == 3) for (int t = 0; t < P::T; t++) fwd_mid<P>(t, tb[t], sm.data());
-    for (int t = 0; t < P::T; t++) centre_real_fwd<P>(t, sm.data());
-    for (int t = 0; t < P::T; t++) centre_real_mix<P>(t, AB.data(), sm.data(), u.data() + (size_t)t * P::E);
+    for (int t = 0; t < P::T; t++) centre_real_fwd_keep<P>(t, sm.data(), u.data() + (size_t)t * P::E);
+    for (int t = 0; t < P::T; t++) centre_real_mix_keep<P>(t, AB.data(), sm.data(), u.data() + (size_t)t * P::E);
     for (int t = 0; t < P::T; t++) centre_real_store<P>(t, sm.data(), u.data() + (size_t)t * P::E);
     if constexpr (P::NPASS == 3) for (int t = 0; t < P::T; t++) inv_mid<P>(t, tb[t], sm.data());
     for (int t = 0; t < P::T; t++) inv_last_real<P>(t, w, tb[t], sm.data());

@@ -263,10 +263,10 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
     if (live) fwd_mid<P>(t, tb, sm);
     __syncwarp();                       // middle passes stay inside the half-warp
   }
-  if (live) centre_real_fwd<P>(t, sm);
+  if (live) centre_real_fwd_keep<P>(t, sm, u);
   asm volatile("griddepcontrol.wait;" ::: "memory");
   group_sync<P, G>(grp);                // mirror bins live in other threads of the group
-  if (live) centre_real_mix<P>(t, reinterpret_cast<const float4 *>(p.spectrum), sm, u);
+  if (live) centre_real_mix_keep<P>(t, reinterpret_cast<const float4 *>(p.spectrum), sm, u);
   group_sync<P, G>(grp);                // every mirror has been read: safe to overwrite
   if (live) centre_real_store<P>(t, sm, u);
   if constexpr (P::NPASS == 3) {
@@ -773,58 +773,6 @@ __device__ __forceinline__ void fwd_first_real_tm(int t, const SegReal &w, float
   static_for<0, R>([&](auto kk) {
     constexpr int k = decltype(kk)::value;
     smb[G::off(k)] = v[k];
-  });
-}
-
-// centre of the real-packed transform with this thread's own bins kept in registers across the
-// barrier (the plain kernel writes them to shared memory for the mirror reads of other threads
-// AND reads its own back afterwards: 32 shared-memory loads per thread that this form saves).
-// step 1: last forward pass; bins to shared memory (others read them as mirrors) and to z[]
-template <class P>
-__device__ __forceinline__ void centre_real_fwd_keep(int t, float2 *sm, float2 *z) {
-  constexpr int R = P::R3;
-  static_for<0, P::E / R>([&](auto jj) {
-    constexpr int j = decltype(jj)::value;
-    int base, bf, k1, k2;
-    centre_locate<P>(t, j, base, bf, k1, k2);
-    auto *smb = sm + pad_pos(base);
-    float2 *v = z + j * R;
-    static_for<0, R>([&](auto rr) {
-      constexpr int r = decltype(rr)::value;
-      v[bitrev(r, ilog2(R))] = smb[r];
-    });
-    dft_inreg<R, false>(v);
-    static_for<0, R>([&](auto kk) {
-      constexpr int k = decltype(kk)::value;
-      smb[k] = v[k];
-    });
-  });
-}
-// step 2 (after a CTA barrier): Z' = alpha*Z + beta*conj(Z_mirror) in place, then the first
-// inverse pass; z[] holds the results in natural order afterwards
-template <class P>
-__device__ __forceinline__ void centre_real_mix_keep(int t, const float4 *AB, const float2 *sm, float2 *z) {
-  constexpr int R = P::R3, JB = P::E / R;
-  static_for<0, JB>([&](auto jj) {
-    constexpr int j = decltype(jj)::value;
-    int base, bf, k1, k2;
-    centre_locate<P>(t, j, base, bf, k1, k2);
-    float2 u[R];
-    static_for<0, R>([&](auto kk) {
-      constexpr int k = decltype(kk)::value;
-      const float2 own = z[j * R + k];
-      const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k))];
-      const float4 ab = AB[(size_t)(k * P::T + t) * JB + j];
-      float2 r = cmul(own, make_float2(ab.x, ab.y));
-      r.x = fmaf(ab.z, zm.x, fmaf(ab.w, zm.y, r.x));          // + beta * conj(zm)
-      r.y = fmaf(ab.w, zm.x, fmaf(-ab.z, zm.y, r.y));
-      u[bitrev(k, ilog2(R))] = r;
-    });
-    dft_inreg<R, true>(u);
-    static_for<0, R>([&](auto kk) {
-      constexpr int k = decltype(kk)::value;
-      z[j * R + k] = u[k];
-    });
   });
 }
 
