@@ -760,8 +760,20 @@ FC_HD void centre_real_fwd_keep(int t, float2 *sm, float2 *z) {
 }
 // step 2 (after a CTA barrier): Z' = alpha*Z + beta*conj(Z_mirror) in place, then the first
 // inverse pass; z[] holds the results in natural order afterwards
+// The coefficients of the first kPre registers of butterfly 0 can be fetched BEFORE the barrier
+// (they do not depend on it) and handed in through `pre`: their L2 latency then hides behind
+// the barrier wait instead of opening the phase.
+constexpr int kRealPre = 8;
 template <class P>
-FC_HD void centre_real_mix_keep(int t, const float4 *AB, const float2 *sm, float2 *z) {
+FC_HD void centre_real_preload(int t, const float4 *AB, float4 *pre) {
+  constexpr int JB = P::E / P::R3;
+  static_for<0, kRealPre>([&](auto kk) {
+    constexpr int k = decltype(kk)::value;
+    pre[k] = AB[(size_t)(k * P::T + t) * JB];
+  });
+}
+template <class P, bool PRE = false>
+FC_HD void centre_real_mix_keep(int t, const float4 *AB, const float2 *sm, float2 *z, const float4 *pre = nullptr) {
   constexpr int R = P::R3, JB = P::E / R;
   static_for<0, JB>([&](auto jj) {
     constexpr int j = decltype(jj)::value;
@@ -772,7 +784,9 @@ FC_HD void centre_real_mix_keep(int t, const float4 *AB, const float2 *sm, float
       constexpr int k = decltype(kk)::value;
       const float2 own = z[j * R + k];
       const float2 zm = sm[pad_pos(mirror_pos<P>(k1, k2, k))];
-      const float4 ab = AB[(size_t)(k * P::T + t) * JB + j];
+      float4 ab;
+      if constexpr (PRE && j == 0 && k < kRealPre) ab = pre[k];
+      else ab = AB[(size_t)(k * P::T + t) * JB + j];
       float2 r = cmul(own, make_float2(ab.x, ab.y));
       r.x = fmaf(ab.z, zm.x, fmaf(ab.w, zm.y, r.x));          // + beta * conj(zm)
       r.y = fmaf(ab.w, zm.x, fmaf(-ab.z, zm.y, r.y));

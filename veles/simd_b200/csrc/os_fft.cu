@@ -843,8 +843,10 @@ __global__ void __launch_bounds__(P::T) os_fused_real_persist_kernel(OsParams p)
     __syncwarp();                       // middle passes stay inside the half-warp
     float2 u[P::E];
     centre_real_fwd_keep<P>(t, sm, u);
+    float4 pre[kRealPre];
+    centre_real_preload<P>(t, AB, pre);  // in flight across the barrier
     __syncthreads();                    // mirror bins live in other threads
-    centre_real_mix_keep<P>(t, AB, sm, u);
+    centre_real_mix_keep<P, true>(t, AB, sm, u, pre);
     __syncthreads();                    // every mirror has been read: safe to overwrite
     centre_real_store<P>(t, sm, u);
     __syncwarp();
