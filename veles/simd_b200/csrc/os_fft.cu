@@ -346,6 +346,32 @@ __device__ __forceinline__ void tm_twiddle_fwd(float2 *v, unsigned set_addr, tme
   tm_apply_fwd<3>(v, b);
 }
 
+// Twiddle factors applied chunk by chunk, each chunk stored as soon as it is done, so that the 32
+// stores of a thread spread over the multiplications instead of leaving in one burst.
+template <class G>
+__device__ __forceinline__ void tm_twiddle_store_fwd(float2 *v, float2 *smb, unsigned set_addr, tmem::Chunk &a,
+                                                     tmem::Chunk &b) {
+  auto store8 = [&](auto cc) {
+    constexpr int c = decltype(cc)::value;
+    static_for<0, 8>([&](auto ii) {
+      constexpr int k = 8 * c + decltype(ii)::value;
+      smb[G::off(k)] = v[k];
+    });
+  };
+  tmem::wait_loads(a, b);
+  tm_apply_fwd<0>(v, a);
+  store8(std::integral_constant<int, 0>{});
+  tmem::load(a, set_addr + 32);
+  tm_apply_fwd<1>(v, b);
+  store8(std::integral_constant<int, 1>{});
+  tmem::load(b, set_addr + 48);
+  tmem::wait_loads(a, b);
+  tm_apply_fwd<2>(v, a);
+  store8(std::integral_constant<int, 2>{});
+  tm_apply_fwd<3>(v, b);
+  store8(std::integral_constant<int, 3>{});
+}
+
 // Forward first pass.  x[inA, inA + park_len) -- zeros where that leaves the signal -- was
 // brought into shared memory (`park`) while the previous pair was being processed: all of
 // segment A and the head of segment B (which starts `step` samples later); the rows of B
@@ -377,12 +403,8 @@ __device__ __forceinline__ void fwd_first_parked_tm(int t, const SegPair &w, flo
     v[bitrev(r, ilog2(R))] = make_float2(va, vb);
   });
   dft_inreg<R, false>(v);
-  tm_twiddle_fwd(v, tw_addr, a, b);
-  before_stores();
-  static_for<0, R>([&](auto kk) {
-    constexpr int k = decltype(kk)::value;
-    smb[G::off(k)] = v[k];
-  });
+  before_stores();          // ahead of the twiddle multiplications, so that the stores mix with them
+  tm_twiddle_store_fwd<G>(v, smb, tw_addr, a, b);
 }
 
 // pairs that cannot be parked (nothing of them inside the signal is bulk-copyable)
@@ -414,12 +436,8 @@ __device__ __forceinline__ void fwd_first_tm(int t, const SegPair &w, float2 *sm
     });
   }
   dft_inreg<R, false>(v);
-  tm_twiddle_fwd(v, tw_addr, a, b);
   before_stores();
-  static_for<0, R>([&](auto kk) {
-    constexpr int k = decltype(kk)::value;
-    smb[G::off(k)] = v[k];
-  });
+  tm_twiddle_store_fwd<G>(v, smb, tw_addr, a, b);
 }
 
 template <class P>
@@ -483,13 +501,17 @@ __device__ __forceinline__ void inv_mid_tm(int t, float2 *sm, unsigned tw_addr) 
   });
 }
 
-template <class P>
-__device__ __forceinline__ void inv_last_regs_tm(int t, const float2 *sm, float2 *v, unsigned tw_addr) {
+// `after_loads` runs once this thread's inputs are out of the transform buffer, before the
+// butterfly network
+template <class P, class F>
+__device__ __forceinline__ void inv_last_regs_tm(int t, const float2 *sm, float2 *v, unsigned tw_addr,
+                                                 F &&after_loads) {
   constexpr int R = P::R1, NB = P::N;
   using G = PassGeom<P, NB, R>;
   int base, npp, bf;
   G::locate(t, 0, base, npp, bf);
   tm_load_twiddled_inv<P, G, R>(sm + pad_pos(base), v, tw_addr);
+  after_loads();
   dft_inreg<R, true>(v);
 }
 
@@ -673,7 +695,10 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
       SegPair w;
       pair_of(item, w);
       float2 v[P::E];
-      inv_last_regs_tm<P>(t, sm, v, tw_addr);
+      // the barrier "every thread has read its last-pass inputs" sits between those reads and
+      // the last butterfly network: the staging stores below then follow the arithmetic that
+      // produces them instead of a barrier that releases all 16 warps' stores at once
+      inv_last_regs_tm<P>(t, sm, v, tw_addr, [&]() { if (!p.accumulate) __syncthreads(); });
       if (!w.accumulate) {
         // Results leave through shared memory and one bulk copy per segment (TMA store): the
         // warps do not wait for the stores to drain, the next pair's first pass computes
@@ -683,7 +708,6 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
         const int phase = (int)((((unsigned long long)(w.out + w.outA)) >> 2) & 3ull);
         const int span = (p.step + 8 + 3) & ~3;
         float *stA = st, *stB = st + span;
-        __syncthreads();                  // every thread has read its last-pass inputs
         stage_outputs<P>(t, v, w.c_off, p.step, phase, stA, stB);
         __syncthreads();
         // per segment: `head` scalar samples up to the next 16-byte boundary, a bulk store of
