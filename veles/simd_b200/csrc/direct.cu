@@ -65,37 +65,50 @@ __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gsrc, i
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
+// 16 taps starting at tap j0 against the 32-sample window [lo | hi] (lo = samples j0 .. j0+15
+// of the thread's row, hi = the next 16): 256 FMAs
+__device__ __forceinline__ void taps16(float (&acc)[kR], const float *gs, int j0, const float (&lo)[16],
+                                       const float (&hi)[16]) {
+#pragma unroll
+  for (int q4 = 0; q4 < 4; q4++) {
+    float4 g = *reinterpret_cast<const float4 *>(gs + j0 + 4 * q4);
+    const float gg[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+#pragma unroll
+      for (int r = 0; r < kR; r++) {
+        const int i = r + 4 * q4 + jj;                   // compile-time: which half of the window
+        acc[r] = fmaf(gg[jj], i < 16 ? lo[i] : hi[i - 16], acc[r]);
+      }
+    }
+  }
+}
+__device__ __forceinline__ void load16(float (&w)[16], const float *src) {
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    float4 v = *reinterpret_cast<const float4 *>(src + 4 * i);
+    w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+  }
+}
+
 // acc[r] += sum_{j < hc} gs[j] * xs[t0 + r + j], r < 16; xrow = xs + padx(t0)
+// The sliding 32-sample window lives in two 16-register halves that swap roles from one block
+// of 16 taps to the next (two blocks per loop trip), so it never has to be shifted.
 __device__ __forceinline__ void accumulate_taps(float (&acc)[kR], const float *gs,
                                                 const float *xrow, int hc) {
   const int hc16 = hc & ~15;
-  float w[32];
-  if (hc16 > 0) {
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      float4 v = *reinterpret_cast<const float4 *>(xrow + 4 * i);
-      w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-    }
+  float wa[16], wb[16];
+  if (hc16 > 0) load16(wa, xrow);
+  int j0 = 0;
+  for (; j0 + 32 <= hc16; j0 += 32) {
+    load16(wb, xrow + ((j0 + 16) >> 4) * 20);
+    taps16(acc, gs, j0, wa, wb);
+    load16(wa, xrow + ((j0 + 32) >> 4) * 20);
+    taps16(acc, gs, j0 + 16, wb, wa);
   }
-  for (int j0 = 0; j0 < hc16; j0 += 16) {
-    const float *xn = xrow + ((j0 + 16) >> 4) * 20;
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      float4 v = *reinterpret_cast<const float4 *>(xn + 4 * i);
-      w[16 + 4 * i] = v.x; w[17 + 4 * i] = v.y; w[18 + 4 * i] = v.z; w[19 + 4 * i] = v.w;
-    }
-#pragma unroll
-    for (int q4 = 0; q4 < 4; q4++) {
-      float4 g = *reinterpret_cast<const float4 *>(gs + j0 + 4 * q4);
-      const float gg[4] = {g.x, g.y, g.z, g.w};
-#pragma unroll
-      for (int jj = 0; jj < 4; jj++) {
-#pragma unroll
-        for (int r = 0; r < kR; r++) acc[r] = fmaf(gg[jj], w[r + 4 * q4 + jj], acc[r]);
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 16; i++) w[i] = w[i + 16];
+  if (j0 < hc16) {                                       // an odd block of 16 taps
+    load16(wb, xrow + ((j0 + 16) >> 4) * 20);
+    taps16(acc, gs, j0, wa, wb);
   }
   // remaining (< 16) taps, four at a time with exact tap predicates
   for (int j0 = hc16; j0 < hc; j0 += 4) {
@@ -203,17 +216,23 @@ __global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
             make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
       }
     }
-    __syncthreads();
-    float *o = ob + n0 + tid;
-    const float *sr = obuf + padx(tid);
-    const int oiters = (cnt - tid + kTPB - 1) / kTPB;
-    if (n0 >= 0) {
-#pragma unroll 4
-      for (int k = 0; k < oiters; k++, o += kTPB, sr += kTPB + kTPB / 4) *o = *sr;
+    // Every warp wrote the 512 consecutive outputs of its own 32 threads and copies exactly
+    // those out again: a warp-level barrier is enough, the CTA keeps a single barrier per tile.
+    __syncwarp();
+    const int wbase = (tid & ~31) * kR + (tid & 31);       // this lane's first output of the warp's 512
+    float *o = ob + n0 + wbase;
+    const float *sr = obuf + padx(wbase);
+    if (n0 >= 0 && cnt == kTile) {
+      // a whole tile: 16 copies per thread at compile-time offsets (32 outputs = 2 padded rows apart)
+#pragma unroll
+      for (int k = 0; k < kR; k++) o[k * 32] = sr[k * 40];
     } else {
-      // tile 0 of a signal whose tiles were shifted for alignment: its first `lead` outputs do not exist
-      for (int k = 0; k < oiters; k++, o += kTPB, sr += kTPB + kTPB / 4)
-        if (n0 + tid + (i64)k * kTPB >= 0) *o = *sr;
+      // last tile of a signal, or tile 0 of a signal whose tiles were shifted for alignment (its
+      // first `lead` outputs do not exist)
+      for (int k = 0; k < kR; k++) {
+        const i64 n = n0 + wbase + k * 32;
+        if (n >= 0 && wbase + k * 32 < cnt) o[k * 32] = sr[k * 40];
+      }
     }
   }
 }
