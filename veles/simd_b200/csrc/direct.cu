@@ -157,12 +157,24 @@ __global__ void __launch_bounds__(kTPB, 6) direct_kernel(DirectParams p) {
       // xi0 is a multiple of 4 and the row starts on a 16-byte boundary: whole 16-byte units,
       // four samples each, never straddling a 16-sample padded row; a unit is inside the signal,
       // outside it (zero-filled), or -- at the signal's end only -- partly inside
-      const int units = (wlen + 3) >> 2;
-      for (int u = tid; u < units; u += kTPB) {
-        const i64 i = xi0 + 4 * (i64)u;
-        const i64 left = p.x_len - i;                      // samples of the signal from i on
-        const int n = i < 0 || left <= 0 ? 0 : (left < 4 ? (int)left : 4);
-        cp_async16(xs + padx(4 * u), n ? xb + i : xb, 4 * n);
+      // The samples that exist are window positions [lo, hi) (clamped to the window; lo is a
+      // multiple of 4 like xi0): one 64-bit computation per tile, 32-bit tests per unit.
+      const int span = 4 * ((wlen + 3) >> 2);
+      const i64 lo64 = -xi0, hi64 = p.x_len - xi0;
+      const int lo = lo64 <= 0 ? 0 : (lo64 < span ? (int)lo64 : span);
+      const int hi = hi64 >= span ? span : (hi64 > 0 ? (int)hi64 : 0);
+      // thread's unit q = 4*tid, then every 4*kTPB samples = 32 padded rows = 5*kTPB floats on
+      const i64 off = xi0 + 4 * tid;
+      float *d = xs + padx(4 * tid);
+      if (lo == 0 && hi == span) {
+        const float *s = xb + off;
+        for (int q = 4 * tid; q < span; q += 4 * kTPB, s += 4 * kTPB, d += 5 * kTPB) cp_async16(d, s, 16);
+      } else {
+        for (int q = 4 * tid; q < span; q += 4 * kTPB, d += 5 * kTPB) {
+          int n = hi - q;
+          n = q < lo || n <= 0 ? 0 : (n < 4 ? n : 4);
+          cp_async16(d, n ? xb + off + (q - 4 * tid) : xb, 4 * n);
+        }
       }
       cp_async_commit();
       return;

@@ -45,6 +45,7 @@ struct OsParams {
   i64 total;                // npairs * batch
   int accumulate;
   i64 prefetch_distance;    // work items between a CTA and its successor on the same SM
+  unsigned per_signal_rcp;  // floor(2^32 / work items per signal) when everything fits 31 bits, else 0
 };
 
 struct SpecParams {
@@ -71,13 +72,18 @@ __device__ __forceinline__ void group_sync(int grp) {
   }
 }
 
-// item -> (signal, unit inside the signal); 32-bit division when the numbers allow it (the
-// 64-bit one costs more than a radix-4 butterfly network on the small plans)
-__device__ __forceinline__ void split_item(i64 item, i64 per_signal, i64 &sig, i64 &unit) {
-  if (((item | per_signal) >> 31) == 0) {
-    const unsigned q = (unsigned)item / (unsigned)per_signal;
+// item -> (signal, unit inside the signal).  The division is by a launch constant: when the
+// numbers fit 31 bits the host passes rcp = floor(2^32 / per_signal) (0xffffffff for 1) and the
+// quotient is umulhi(item, rcp), at most one too small -- five instructions instead of the
+// two dozen of a 32-bit division, and the 64-bit one costs more than a radix-4 butterfly network.
+__device__ __forceinline__ void split_item(i64 item, i64 per_signal, unsigned rcp, i64 &sig, i64 &unit) {
+  if (rcp != 0) {
+    const unsigned n = (unsigned)item, d = (unsigned)per_signal;
+    unsigned q = __umulhi(n, rcp);
+    unsigned r = n - q * d;
+    if (r >= d) { q++; r -= d; }
     sig = q;
-    unit = (unsigned)item - q * (unsigned)per_signal;
+    unit = r;
   } else {
     sig = item / per_signal;
     unit = item - sig * per_signal;
@@ -125,13 +131,14 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
   SegPair w;
   TwBases<P> tb;
   HRegs<P> hr;
-  if (t == 0) {
+  if (threadIdx.x < G) {
     // Pull the input of the CTA that will follow this one on the SM into L2 while this CTA
     // computes (CTAs are dispatched in index order, one wave = p.prefetch_distance items).
-    const i64 nxt = item + p.prefetch_distance;
+    // The first G threads do it, one group's item each, so that one warp pays for it.
+    const i64 nxt = (i64)blockIdx.x * G + threadIdx.x + p.prefetch_distance;
     if (p.prefetch_distance > 0 && nxt < p.total) {
       i64 nb, nsa;
-      split_item(nxt, p.npairs, nb, nsa);
+      split_item(nxt, p.npairs, p.per_signal_rcp, nb, nsa);
       nsa *= 2;
       i64 lo = nsa * p.step + p.in_shift;
       i64 hi = lo + p.step + P::N;
@@ -149,7 +156,7 @@ __global__ void __launch_bounds__(P::T *G) os_fused_kernel(OsParams p) {
   if (live) {
     load_twiddle_bases<P>(t, p.tw, tb);
     i64 b, sa;
-    split_item(item, p.npairs, b, sa);
+    split_item(item, p.npairs, p.per_signal_rcp, b, sa);
     sa *= 2;
     w.x = p.x + b * p.x_stride;
     w.x_len = p.x_len;
@@ -225,11 +232,11 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
   SegReal w;
   TwBases<P> tb;
   float2 u[P::E];
-  if (t == 0) {
-    const i64 nxt = item + p.prefetch_distance;
+  if (threadIdx.x < G) {
+    const i64 nxt = (i64)blockIdx.x * G + threadIdx.x + p.prefetch_distance;
     if (p.prefetch_distance > 0 && nxt < p.total) {
       i64 nb, nsg;
-      split_item(nxt, p.nseg, nb, nsg);
+      split_item(nxt, p.nseg, p.per_signal_rcp, nb, nsg);
       i64 lo = nsg * p.step + p.in_shift;
       i64 hi = lo + 2 * P::N;
       if (lo < 0) lo = 0;
@@ -246,7 +253,7 @@ __global__ void __launch_bounds__(P::T *G) os_fused_real_kernel(OsParams p) {
   if (live) {
     load_twiddle_bases<P>(t, p.tw, tb);
     i64 b, sg;
-    split_item(item, p.nseg, b, sg);
+    split_item(item, p.nseg, p.per_signal_rcp, b, sg);
     w.x = p.x + b * p.x_stride;
     w.x_len = p.x_len;
     w.in0 = sg * p.step + p.in_shift;
@@ -938,6 +945,12 @@ void launch_fused(const OsParams &p, cudaStream_t stream, bool after_spectrum) {
       wave[dev] = per_sm * sms > 0 ? per_sm * sms : 1;
     }
     q.prefetch_distance = (i64)(dev < 16 ? wave[dev] : 148) * G;
+  }
+  {
+    const i64 per_signal = REAL ? p.nseg : p.npairs;
+    q.per_signal_rcp = 0;
+    if (per_signal > 0 && per_signal < (1LL << 31) && p.total + q.prefetch_distance < (1LL << 31))
+      q.per_signal_rcp = per_signal == 1 ? 0xffffffffu : (unsigned)((1ULL << 32) / (unsigned long long)per_signal);
   }
   if (after_spectrum) {
     // launched right behind the spectrum kernel: let it start before that kernel finishes
