@@ -289,6 +289,56 @@ def test_persistent_kernel_signal_edges(simd, oracle, monkeypatch, B, xl, hl, x_
         assert torch.isnan(ybuf[:, xl + hl - 1:]).all()
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_random_batched_shapes(simd, oracle, seed):
+    """Seeded random batches through convolve_batch / cross_correlate_batch on pitched device buffers
+    whose rows start at every 4-byte phase (the direct kernel stages 16-byte units only when rows are
+    16-byte aligned; the transform kernels pick bulk or scalar stores by the same test), forced onto
+    the direct kernel and onto overlap-save in turn.  Row padding must stay untouched."""
+    import torch
+    simd.use_torch_stream()
+    rng = np.random.default_rng(9000 + seed)
+    B = int(rng.integers(1, 40))
+    hl = int(rng.choice([1, 2, 3, 7, 16, 31, 64, 100, 257, 700]))
+    xl = int(rng.integers(max(2 * hl + 2, 8), 60000 if seed % 3 else 400000))
+    ol = xl + hl - 1
+    x_pitch = xl + int(rng.integers(0, 9))
+    o_pitch = ol + int(rng.integers(0, 9))
+    x_off, o_off = int(rng.integers(0, 4)), int(rng.integers(0, 4))
+    corr = bool(seed & 1)
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    xbuf = torch.rand((B * x_pitch + 4,), generator=g, device="cuda") * 2 - 1
+    h = torch.rand((hl,), generator=g, device="cuda") * 2 - 1
+    hn = h.cpu().numpy()
+    xrows = xbuf[x_off:x_off + B * x_pitch].view(B, x_pitch)
+    call = simd.lib.cross_correlate_batch if corr else simd.lib.convolve_batch
+    rows = sorted(set([0, B - 1, B // 2]))
+    want = {b: oracle.convolve_fft(xrows[b, :xl].cpu().numpy().copy(), hn, corr) for b in rows}
+    for alg in ("brute", "os"):
+        ybuf = torch.full((B * o_pitch + 4,), float("nan"), device="cuda")
+        yrows = ybuf[o_off:o_off + B * o_pitch].view(B, o_pitch)
+        hd = simd.ConvolutionHandle()
+        hd.x_length, hd.h_length = xl, hl
+        if alg == "brute":
+            hd.algorithm = simd.ALG_BRUTE_FORCE
+            call(hd, xrows.data_ptr(), x_pitch, h.data_ptr(), yrows.data_ptr(), o_pitch, B)
+        else:
+            with simd.Handle(xl, hl, "_overlap_save", corr) as inner:
+                hd.algorithm = simd.ALG_OVERLAP_SAVE
+                hd.handle.os = inner.handle
+                call(hd, xrows.data_ptr(), x_pitch, h.data_ptr(), yrows.data_ptr(), o_pitch, B)
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        for b in rows:
+            xb = xrows[b, :xl].cpu().numpy().copy()
+            check(yrows[b, :ol].cpu().numpy(), want[b], xb, hn,
+                  f"seed {seed} {alg} B={B} x={xl} h={hl} corr={corr} row {b}")
+        assert not torch.isnan(yrows[:, :ol]).any()
+        if o_pitch > ol:
+            assert torch.isnan(yrows[:, ol:]).all()
+        assert torch.isnan(ybuf[:o_off]).all() and torch.isnan(ybuf[o_off + B * o_pitch:]).all()
+
+
 def test_long_signal_c5_shape(simd, oracle):
     """BASELINE config 5 at full size: x = 2^30 samples, h = 8192, on one GPU.  Windows of
     the result are checked against a float64 direct convolution of the matching x window."""
