@@ -43,6 +43,8 @@ WORKLOADS = {
     "c3": ("convolve", 4096, 16384, 64, "batched convolve 4096 x 16384, h=64"),
     "c4": ("convolve", 1024, 262144, 4096, "batched convolve 1024 x 262144, h=4096"),
     "c5": ("convolve", 1, 2 ** 30, 8192, "single long signal x=2^30, h=8192"),
+    # not a BASELINE config: the C3 batch with a 16-tap filter, where the direct kernel is HBM-bound
+    "c3h16": ("convolve", 4096, 16384, 16, "batched convolve 4096 x 16384, h=16 (direct kernel, HBM-bound regime)"),
     # SURVEY 8(f) rank 1 (not a BASELINE config): extrema of a 2^28-sample series
     "peaks": ("detect_peaks", 1, 2 ** 28, 0, "detect_peaks (both kinds) on 2^28 uniform random samples"),
     "minmax": ("minmax1D", 1, 2 ** 28, 0, "minmax1D on 2^28 uniform random samples"),
