@@ -761,7 +761,10 @@ __global__ void __launch_bounds__(P::T) os_fused_persist_kernel(OsParams p) {
 // largest stall), so what helped the paired kernel hurts here -- measured on one GPU, C5:
 //   plain kernel 4.670 ms | + Tensor-Memory twiddles, persistent 4.256 | + results staged in
 //   shared memory and bulk-stored 4.504 | + the first 5 of 16 {alpha, beta} rows resident in
-//   shared memory 4.438 | both 4.583.
+//   shared memory 4.438 | both 4.583.  Against the final kernel (4.03 ms): the first 22 of 32
+//   input rows of the next segment parked in shared memory by a bulk copy (the paired kernel's
+//   +5 %) 4.47 ms -- 22 more shared-memory reads per thread cost more than the global loads they
+//   replace, whose latency the L2 prefetch already hides.
 template <class P>
 __device__ __forceinline__ void fwd_first_real_tm(int t, const SegReal &w, float2 *sm, unsigned tw_addr,
                                                   bool buffer_in_use) {
