@@ -1077,6 +1077,25 @@ const float2 *b200_twiddles(int n_fft) {
   return dptr;
 }
 
+// Up to 15 extra leading samples per segment make the first useful circular sample a multiple of
+// 16 -- taken only when the number of segment pairs stays the same, i.e. when it is free.  The
+// last pass holds circular samples n + 16r (or a coarser stride) in register r of the thread at
+// position n: with c_off a multiple of 16 the test "is this register an output" is the same for
+// every thread of a warp, so the store sequence is entered once instead of once per distinct
+// first register (C3, c_off 63 -> 64: two passes through the stores became one), and segment
+// inputs and outputs start on 64-byte boundaries of their rows.
+static void align_segments(OsParams &op, i64 out_len) {
+  const int e = (16 - (op.c_off & 15)) & 15;
+  const int step2 = op.step - e;
+  if (e == 0 || step2 <= 0) return;
+  const i64 pairs1 = ((out_len + op.step - 1) / op.step + 1) / 2;
+  const i64 pairs2 = ((out_len + step2 - 1) / step2 + 1) / 2;
+  if (pairs2 != pairs1) return;
+  op.in_shift -= e;
+  op.c_off += e;
+  op.step = step2;
+}
+
 void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part_taps,
                          const DevJob &job, bool single_segment, cudaStream_t stream) {
   if (job.batch <= 0 || job.out_len <= 0) return;
@@ -1109,6 +1128,7 @@ void b200_os_launch_with(const float2 *tw, float2 *spectrum, int n_fft, int part
                      "single-segment FFT does not fit the transform");                 \
       } else {                                                                         \
         op.in_shift = j0 - job.pad; op.c_off = taps - 1; op.step = PLAN::N - taps + 1; \
+        if (PLAN::N < 16384) align_segments(op, job.out_len);                          \
       }                                                                                \
       op.nseg = (job.out_len + op.step - 1) / op.step;                                 \
       op.npairs = (op.nseg + 1) / 2;                                                   \
