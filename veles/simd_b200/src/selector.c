@@ -14,10 +14,13 @@
 #include <stdlib.h>
 #include "../csrc/b200_internal.h"
 
-/* Cost model fitted to B200 timings (profiles/selector_sweep_r01.md, device-resident data).
+/* Cost model fitted to B200 timings (profiles/selector_sweep_r02.md, device-resident data).
  *
- *   direct kernel        t = 9 us + 4.5e-8 us per multiply-add        (one launch)
- *   fused overlap-save   t = 15 us + c(N) * outputs/67.1e6 * N/(N-taps+1) per partition
+ *   direct kernel        t = 9 us + max(1.64e-6 us per output                      (HBM floor)
+ *                                       0.9e-6 us per output + 3.5e-8 us per multiply-add)
+ *                        (one launch; 3.8e-8 above 512 taps, where fewer CTAs fit an SM)
+ *   fused overlap-save   t = 15 us + max(1.85e-6 us per output                     (HBM floor)
+ *                                        c(N) * outputs/67.1e6 * N/(N-taps+1) per partition)
  *                        (two launches; c(N) = us per 67.1e6 outputs at 100 % segment use)
  *
  * c(N) is not monotone in N: transforms up to 2048 points run many CTAs per SM and overlap
@@ -25,10 +28,14 @@
 static const struct { int n; double c; double real_ratio; } kFusedCost[] = {
   /* N, paired cost c(N), cost of a real-packed transform relative to a paired one
    * (tools/real_ratio.py; 256 / 512 extrapolated from the C3 shape) */
-  {256, 111.0, 1.6}, {512, 147.0, 1.5}, {1024, 150.0, 1.34}, {2048, 149.0, 1.20},
+  {256, 104.0, 1.6}, {512, 147.0, 1.5}, {1024, 150.0, 1.34}, {2048, 149.0, 1.20},
   {4096, 192.0, 1.12}, {8192, 203.0, 1.39}, {16384, 237.0, 1.35},
 };
-#define B200_DIRECT_US_PER_MAC 4.5e-8
+#define B200_DIRECT_US_PER_MAC 3.5e-8
+#define B200_DIRECT_US_PER_MAC_LONG 3.8e-8     /* more than 512 taps */
+#define B200_DIRECT_US_PER_OUTPUT 0.9e-6
+#define B200_DIRECT_FLOOR_US_PER_OUTPUT 1.64e-6
+#define B200_FUSED_FLOOR_US_PER_OUTPUT 1.85e-6
 #define B200_DIRECT_LAUNCH_US 9.0
 #define B200_FUSED_LAUNCH_US 15.0
 
@@ -41,7 +48,9 @@ static double fused_cost_us(int n, double c, long long h_len, long long out_len,
   double nseg = (double)((out_len + (long long)step - 1) / (long long)step);
   double pairs = (double)(((long long)nseg + 1) / 2);
   double points = pairs * 2.0 * n * (double)batch;       /* real samples transformed */
-  return B200_FUSED_LAUNCH_US + (double)parts * c * points / 67.1e6;
+  double work = (double)parts * c * points / 67.1e6;
+  double floor_us = B200_FUSED_FLOOR_US_PER_OUTPUT * (double)out_len * (double)batch;
+  return B200_FUSED_LAUNCH_US + (work > floor_us ? work : floor_us);
 }
 
 /* Transform length for an impulse response of h_len taps producing out_len outputs per
@@ -105,7 +114,12 @@ ConvolutionAlgorithm simd_b200_select_algorithm_batch(size_t x_length, size_t h_
   /* fewer tiles than SMs: the small-problem kernel (512-output tiles, 4 outputs per thread)
    * runs instead; its serial chain per thread is a quarter as long */
   if (tiles < 148.0 && h_length <= 1024) per_wave_us = (double)h_length * 2.1e-3;
-  double direct_work = B200_DIRECT_US_PER_MAC * (double)batch * (double)x_length * (double)h_length;
+  double outputs = (double)out_len * (double)batch;
+  double direct_work = B200_DIRECT_US_PER_OUTPUT * outputs +
+                       (h_length > 512 ? B200_DIRECT_US_PER_MAC_LONG : B200_DIRECT_US_PER_MAC) *
+                           (double)batch * (double)x_length * (double)h_length;
+  if (B200_DIRECT_FLOOR_US_PER_OUTPUT * outputs > direct_work)
+    direct_work = B200_DIRECT_FLOOR_US_PER_OUTPUT * outputs;
   if (waves * per_wave_us > direct_work) direct_work = waves * per_wave_us;
   double direct = B200_DIRECT_LAUNCH_US + direct_work;
   int n = b200_os_pick_n((long long)h_length, out_len);
